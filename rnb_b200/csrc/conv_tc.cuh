@@ -1,0 +1,57 @@
+// Parameters of the tcgen05 implicit-GEMM convolution (shared by host planner and kernel).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rnb {
+
+constexpr int kMaxTaps = 32;
+constexpr int kTileM = 128;          // output positions per tile = TMEM lanes
+constexpr int kMaxBlockN = 256;      // accumulator columns per tile
+constexpr int kTmemCols = 512;       // two accumulator buffers
+constexpr int kConvThreads = 192;    // warp0 TMA, warp1 MMA, warps2-5 epilogue
+constexpr int kStagingBytes = 16384; // one 128 x 64 bf16 output sub-tile
+constexpr int kSmemLimit = 232448;   // 227 KB
+
+// One output tile is a box of 128 output positions (bw x bh x bt x bb, powers of two) by up to
+// block_n output channels.  K runs over `num_taps` filter taps times cin_pad input channels; tap i
+// reads the activation view a_map[tap_map[i]] shifted by (tap_dw, tap_dh, tap_dt) positions.
+struct ConvTcParams {
+  alignas(64) CUtensorMap a_map[4];  // activation views, dims (C, W, H, T, B), bf16
+  alignas(64) CUtensorMap b_map;     // packed weights, dims (K_total, N_rows), bf16, K-major
+  alignas(64) CUtensorMap d_map;     // output, dims (C, W, H, T, B), bf16
+  const float* scale;                // per output channel, length n_tiles*block_n
+  const float* shift;
+  const __nv_bfloat16* residual;     // same layout as the output, or nullptr
+  int num_taps;
+  int cin_pad;      // input channels per tap (multiple of 16)
+  int bk;           // K elements per pipeline stage: 64 (128-byte swizzle) or 32 (64-byte swizzle)
+  int kb_per_tap;   // ceil(cin_pad / bk)
+  int lbw, lbh, lbt;  // log2 of the position box; bb = 128 >> (lbw + lbh + lbt)
+  int tiles_w, tiles_h, tiles_t, tiles_b;
+  int n_tiles, block_n;
+  int Wo, Ho, To, B;  // output extent
+  int cout_pad;       // stored output channels (multiple of 16)
+  int relu;
+  int num_stages;
+  int8_t tap_map[kMaxTaps];
+  int8_t tap_dw[kMaxTaps];
+  int8_t tap_dh[kMaxTaps];
+  int8_t tap_dt[kMaxTaps];
+  int16_t tap_coff[kMaxTaps];  // channel offset inside the activation view
+  int32_t tap_koff[kMaxTaps];  // K offset inside the packed weights
+};
+
+inline int conv_tc_stage_bytes(int bk, int block_n) { return (kTileM + block_n) * bk * 2; }
+
+// Dynamic shared memory the kernel needs for a given configuration.
+inline int conv_tc_smem_bytes(int bk, int block_n, int stages) {
+  return 1024 /*alignment slack*/ + stages * conv_tc_stage_bytes(bk, block_n) + 2 * kStagingBytes +
+         256 /*barriers*/;
+}
+
+cudaError_t launch_conv_tc(const ConvTcParams& p, int num_sms, cudaStream_t stream);
+
+}  // namespace rnb

@@ -1,0 +1,295 @@
+#include "plan.cuh"
+
+#include <string.h>
+
+#include <mutex>
+
+namespace rnb {
+
+uint16_t f32_to_bf16_bits(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);  // NaN
+  const uint32_t lsb = (u >> 16) & 1u;
+  u += 0x7fffu + lsb;  // round to nearest even
+  return (uint16_t)(u >> 16);
+}
+
+float bf16_bits_to_f32(uint16_t b) {
+  const uint32_t u = (uint32_t)b << 16;
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+
+void pack_conv_weights_tc(const ConvGeom& g, const float* w, std::vector<uint16_t>* packed) {
+  const int kp = g.k_total();
+  const int cp = g.cin_pad();
+  packed->assign((size_t)g.cout_pad() * kp, 0);
+  for (int n = 0; n < g.cout; ++n) {
+    uint16_t* row = packed->data() + (size_t)n * kp;
+    for (int c = 0; c < g.cin; ++c)
+      for (int dt = 0; dt < g.kt; ++dt)
+        for (int dh = 0; dh < g.kh; ++dh)
+          for (int dw = 0; dw < g.kw; ++dw) {
+            const float v = w[((((size_t)n * g.cin + c) * g.kt + dt) * g.kh + dh) * g.kw + dw];
+            size_t k;
+            if (g.stem_unfolded) {
+              k = (size_t)dh * cp + dw * 4 + c;  // filter row -> tap; (column, channel) -> K
+            } else {
+              k = (size_t)((dt * g.kh + dh) * g.kw + dw) * cp + c;
+            }
+            row[k] = f32_to_bf16_bits(v);
+          }
+  }
+}
+
+void pack_conv_weights_ref(const ConvGeom& g, const float* w, std::vector<float>* packed) {
+  packed->assign((size_t)g.kt * g.kh * g.kw * g.cin * g.cout, 0.f);
+  for (int n = 0; n < g.cout; ++n)
+    for (int c = 0; c < g.cin; ++c)
+      for (int dt = 0; dt < g.kt; ++dt)
+        for (int dh = 0; dh < g.kh; ++dh)
+          for (int dw = 0; dw < g.kw; ++dw)
+            (*packed)[((((size_t)dt * g.kh + dh) * g.kw + dw) * g.cin + c) * g.cout + n] =
+                w[((((size_t)n * g.cin + c) * g.kt + dt) * g.kh + dh) * g.kw + dw];
+}
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn(std::string* err) {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  static std::string once_err;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q);
+    if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || p == nullptr) {
+      once_err = std::string("cuTensorMapEncodeTiled not available: ") + cudaGetErrorString(e);
+      (void)cudaGetLastError();
+    } else {
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+  });
+  if (!fn && err) *err = once_err;
+  return fn;
+}
+
+// bf16 tensor map of rank `rank`; dims/box innermost first; strides in BYTES for dims 1..rank-1
+bool encode_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+                 const uint64_t* strides, const uint32_t* box, int swizzle_bytes, std::string* err) {
+  EncodeTiledFn fn = get_encode_fn(err);
+  if (!fn) return false;
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t bdim[5], estr[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    bdim[i] = box[i];
+    estr[i] = 1;
+  }
+  for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides[i];
+  const CUtensorMapSwizzle swz =
+      swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base),
+                  gdim, gstr, bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    if (err) {
+      char buf[512];
+      snprintf(buf, sizeof buf,
+               "cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu %llu %llu %llu %llu] box "
+               "[%u %u %u %u %u] stride0 %llu swizzle %d base %p",
+               (int)r, rank, (unsigned long long)gdim[0], (unsigned long long)(rank > 1 ? gdim[1] : 0),
+               (unsigned long long)(rank > 2 ? gdim[2] : 0), (unsigned long long)(rank > 3 ? gdim[3] : 0),
+               (unsigned long long)(rank > 4 ? gdim[4] : 0), bdim[0], rank > 1 ? bdim[1] : 0,
+               rank > 2 ? bdim[2] : 0, rank > 3 ? bdim[3] : 0, rank > 4 ? bdim[4] : 0,
+               (unsigned long long)(rank > 1 ? gstr[0] : 0), swizzle_bytes, base);
+      *err = buf;
+    }
+    return false;
+  }
+  return true;
+}
+
+int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// position box (bw, bh, bt, bb), powers of two with product 128, minimising the number of tiles
+void choose_box(int Wo, int Ho, int To, int B, int* lbw, int* lbh, int* lbt) {
+  long long best = -1;
+  int bw_ = 0, bh_ = 0, bt_ = 0;
+  for (int a = 0; a <= 7; ++a)
+    for (int b = 0; a + b <= 7; ++b)
+      for (int c = 0; a + b + c <= 7; ++c) {
+        const int d = 7 - a - b - c;
+        const long long tiles = (long long)ceil_div(Wo, 1 << a) * ceil_div(Ho, 1 << b) *
+                                ceil_div(To, 1 << c) * ceil_div(B, 1 << d);
+        // fewer tiles first; then longer contiguous runs (w, then h, then t)
+        const long long key = tiles * 4096 - (a * 64 + b * 8 + c);
+        if (best < 0 || key < best) {
+          best = key;
+          bw_ = a;
+          bh_ = b;
+          bt_ = c;
+        }
+      }
+  *lbw = bw_;
+  *lbh = bh_;
+  *lbt = bt_;
+}
+
+struct View {
+  int pw, ph, pt;
+};
+
+}  // namespace
+
+bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
+                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* scale,
+                          const float* shift, const __nv_bfloat16* residual, bool relu, int num_sms,
+                          ConvTcParams* out, std::string* err) {
+  ConvTcParams& p = *out;
+  memset(&p, 0, sizeof p);
+  const int cp = g.cin_pad();
+  const int np = g.cout_pad();
+  for (int s : {g.st, g.sh, g.sw})
+    if (s != 1 && s != 2) {
+      if (err) *err = "conv_tc: only strides 1 and 2 are supported";
+      return false;
+    }
+  if ((g.sw == 2 && (g.Wi & 1)) || (g.sh == 2 && (g.Hi & 1)) || (g.st == 2 && (g.Ti & 1))) {
+    if (err) *err = "conv_tc: a strided dimension must have even extent";
+    return false;
+  }
+  p.scale = scale;
+  p.shift = shift;
+  p.residual = residual;
+  p.relu = relu ? 1 : 0;
+  p.cin_pad = cp;
+  p.bk = g.stem_unfolded ? 32 : 64;
+  p.kb_per_tap = ceil_div(cp, p.bk);
+  p.Wo = g.Wo;
+  p.Ho = g.Ho;
+  p.To = g.To;
+  p.B = B;
+  p.cout_pad = np;
+
+  choose_box(g.Wo, g.Ho, g.To, B, &p.lbw, &p.lbh, &p.lbt);
+  const int bw = 1 << p.lbw, bh = 1 << p.lbh, bt = 1 << p.lbt, bb = 128 >> (p.lbw + p.lbh + p.lbt);
+  p.tiles_w = ceil_div(g.Wo, bw);
+  p.tiles_h = ceil_div(g.Ho, bh);
+  p.tiles_t = ceil_div(g.To, bt);
+  p.tiles_b = ceil_div(B, bb);
+  const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b;
+
+  // channel tiling: one tile if it fits the accumulator, otherwise multiples of 64 channels so
+  // that the 64-channel output sub-tiles of neighbouring tiles never overlap
+  if (np <= kMaxBlockN) {
+    p.block_n = np;
+    p.n_tiles = 1;
+  } else {
+    const int nt = ceil_div(np, kMaxBlockN);
+    p.block_n = round_up(ceil_div(np, nt), 64);
+    p.n_tiles = ceil_div(np, p.block_n);
+  }
+  // small layers: more, narrower tiles until every SM has one
+  while (m_tiles * p.n_tiles < num_sms && p.block_n > 64) {
+    p.block_n = round_up(p.block_n, 64) - 64;
+    p.n_tiles = ceil_div(np, p.block_n);
+  }
+  const int stage_bytes = conv_tc_stage_bytes(p.bk, p.block_n);
+  int stages = (kSmemLimit - 1024 - 2 * kStagingBytes - 256) / stage_bytes;
+  if (stages > 8) stages = 8;
+  if (stages < 2) {
+    if (err) *err = "conv_tc: pipeline does not fit in shared memory";
+    return false;
+  }
+  p.num_stages = stages;
+
+  // ---- taps and activation views
+  std::vector<View> views;
+  auto view_index = [&](int pw, int ph, int pt) {
+    for (size_t i = 0; i < views.size(); ++i)
+      if (views[i].pw == pw && views[i].ph == ph && views[i].pt == pt) return (int)i;
+    views.push_back({pw, ph, pt});
+    return (int)views.size() - 1;
+  };
+  auto split = [](int off, int stride, int* par, int* shift) {
+    if (stride == 1) {
+      *par = 0;
+      *shift = off;
+    } else {
+      *par = ((off % 2) + 2) % 2;
+      *shift = (off - *par) / 2;
+    }
+  };
+  int ntap = 0;
+  for (int dt = 0; dt < g.kt; ++dt)
+    for (int dh = 0; dh < g.kh; ++dh)
+      for (int dw = 0; dw < (g.stem_unfolded ? 1 : g.kw); ++dw) {
+        if (ntap >= kMaxTaps) {
+          if (err) *err = "conv_tc: too many filter taps";
+          return false;
+        }
+        int pw = 0, ph = 0, pt = 0, sw_ = 0, sh_ = 0, st_ = 0;
+        split(dt - g.pt, g.st, &pt, &st_);
+        split(dh - g.ph, g.sh, &ph, &sh_);
+        if (!g.stem_unfolded) split(dw - g.pw, g.sw, &pw, &sw_);
+        p.tap_map[ntap] = (int8_t)view_index(pw, ph, pt);
+        p.tap_dw[ntap] = (int8_t)sw_;
+        p.tap_dh[ntap] = (int8_t)sh_;
+        p.tap_dt[ntap] = (int8_t)st_;
+        p.tap_coff[ntap] = 0;
+        p.tap_koff[ntap] = ntap * cp;
+        ++ntap;
+      }
+  p.num_taps = ntap;
+  if (views.size() > 4) {
+    if (err) *err = "conv_tc: more than four strided input views";
+    return false;
+  }
+
+  // ---- tensor maps
+  const int swz = p.bk * 2;
+  // input row pitch: the unfolded stem stores Wo groups of 32 per image row
+  const uint64_t in_w = g.stem_unfolded ? (uint64_t)g.Wo : (uint64_t)g.Wi;
+  const uint64_t in_c = (uint64_t)cp;
+  const int eff_sw = g.stem_unfolded ? 1 : g.sw;
+  for (size_t v = 0; v < views.size(); ++v) {
+    const View& vw = views[v];
+    const __nv_bfloat16* base =
+        x + ((size_t)vw.pt * g.Hi * in_w + (size_t)vw.ph * in_w + (size_t)vw.pw) * in_c;
+    const uint64_t dims[5] = {in_c, (uint64_t)((in_w - vw.pw + eff_sw - 1) / eff_sw),
+                              (uint64_t)((g.Hi - vw.ph + g.sh - 1) / g.sh),
+                              (uint64_t)((g.Ti - vw.pt + g.st - 1) / g.st), (uint64_t)B};
+    const uint64_t strides[4] = {(uint64_t)eff_sw * in_c * 2, (uint64_t)g.sh * in_w * in_c * 2,
+                                 (uint64_t)g.st * g.Hi * in_w * in_c * 2,
+                                 (uint64_t)g.Ti * g.Hi * in_w * in_c * 2};
+    const uint32_t box[5] = {(uint32_t)p.bk, (uint32_t)bw, (uint32_t)bh, (uint32_t)bt, (uint32_t)bb};
+    if (!encode_bf16(&p.a_map[v], base, 5, dims, strides, box, swz, err)) return false;
+  }
+  for (size_t v = views.size(); v < 4; ++v) p.a_map[v] = p.a_map[0];
+  {
+    const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)np};
+    const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
+    const uint32_t box[2] = {(uint32_t)p.bk, (uint32_t)p.block_n};
+    if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, swz, err)) return false;
+  }
+  {
+    const uint64_t dims[5] = {(uint64_t)np, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)g.To,
+                              (uint64_t)B};
+    const uint64_t strides[4] = {(uint64_t)np * 2, (uint64_t)g.Wo * np * 2,
+                                 (uint64_t)g.Ho * g.Wo * np * 2,
+                                 (uint64_t)g.To * g.Ho * g.Wo * np * 2};
+    const uint32_t box[5] = {64u, (uint32_t)bw, (uint32_t)bh, (uint32_t)bt, (uint32_t)bb};
+    if (!encode_bf16(&p.d_map, y, 5, dims, strides, box, 128, err)) return false;
+  }
+  return true;
+}
+
+}  // namespace rnb

@@ -1,0 +1,54 @@
+// Host-side planning for the tcgen05 convolution: geometry -> tile shape, tap table, TMA tensor
+// maps, packed weights.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "conv_tc.cuh"
+
+namespace rnb {
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+inline int pad16(int c) { return round_up(c, 16); }
+
+// One Conv3d over a channels-last activation (B, Ti, Hi, Wi, cin_pad) -> (B, To, Ho, Wo, cout_pad).
+struct ConvGeom {
+  int Ti = 1, Hi = 1, Wi = 1, cin = 0;
+  int To = 1, Ho = 1, Wo = 1, cout = 0;
+  int kt = 1, kh = 1, kw = 1;
+  int st = 1, sh = 1, sw = 1;
+  int pt = 0, ph = 0, pw = 0;
+  // stem: the input is the "unfolded" layout of kernels.cuh (B, Ti, Hi, Wo, 32) and only the
+  // filter rows remain as taps
+  bool stem_unfolded = false;
+
+  int cin_pad() const { return stem_unfolded ? 32 : pad16(cin); }
+  int cout_pad() const { return pad16(cout); }
+  int num_taps() const { return stem_unfolded ? kh : kt * kh * kw; }
+  int k_total() const { return num_taps() * cin_pad(); }
+  long long in_elems(int B) const {
+    return stem_unfolded ? (long long)B * Ti * Hi * Wo * 32 : (long long)B * Ti * Hi * Wi * cin_pad();
+  }
+  long long out_elems(int B) const { return (long long)B * To * Ho * Wo * cout_pad(); }
+  double flops(int B) const {  // 2 x MACs, zero-pad taps counted, real channels only
+    return 2.0 * B * To * Ho * Wo * (double)cout * cin * kt * kh * kw;
+  }
+};
+
+// torch weight (cout, cin, kt, kh, kw) fp32 -> K-major bf16 rows (cout_pad, k_total)
+void pack_conv_weights_tc(const ConvGeom& g, const float* w, std::vector<uint16_t>* packed);
+
+// torch weight (cout, cin, kt, kh, kw) -> (kt, kh, kw, cin, cout) fp32 for the direct convolution
+void pack_conv_weights_ref(const ConvGeom& g, const float* w, std::vector<float>* packed);
+
+// Fill `out` for a batch of B clips.  All pointers are device pointers.  Returns false and sets
+// *err on failure (unsupported geometry or a tensor-map encoding error).
+bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
+                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* scale,
+                          const float* shift, const __nv_bfloat16* residual, bool relu, int num_sms,
+                          ConvTcParams* out, std::string* err);
+
+uint16_t f32_to_bf16_bits(float f);
+float bf16_bits_to_f32(uint16_t b);
+
+}  // namespace rnb

@@ -1,0 +1,304 @@
+// Standalone B200 check of the tcgen05 convolution against the fp32 direct convolution, on the
+// geometries R(2+1)D uses.  Build: make -C rnb_b200/csrc test_conv ; run: ./test_conv [perf_batch]
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include <string>
+#include <vector>
+
+#include "conv_tc.cuh"
+#include "kernels.cuh"
+#include "plan.cuh"
+
+using namespace rnb;
+
+#define CK(x)                                                                      \
+  do {                                                                             \
+    cudaError_t e_ = (x);                                                          \
+    if (e_ != cudaSuccess) {                                                       \
+      printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); \
+      exit(2);                                                                     \
+    }                                                                              \
+  } while (0)
+
+static uint32_t rng_state = 12345;
+static float frand() {  // uniform (-1, 1)
+  rng_state = rng_state * 1664525u + 1013904223u;
+  return ((rng_state >> 8) & 0xffff) / 32768.f - 1.f;
+}
+static float bf16_round(float f) { return bf16_bits_to_f32(f32_to_bf16_bits(f)); }
+
+struct Case {
+  const char* name;
+  ConvGeom g;
+  int B;
+  bool relu, residual;
+};
+
+static ConvGeom geom(int Ti, int Hi, int Wi, int cin, int cout, int kt, int kh, int kw, int st,
+                     int sh, int sw, int pt, int ph, int pw) {
+  ConvGeom g;
+  g.Ti = Ti; g.Hi = Hi; g.Wi = Wi; g.cin = cin; g.cout = cout;
+  g.kt = kt; g.kh = kh; g.kw = kw; g.st = st; g.sh = sh; g.sw = sw; g.pt = pt; g.ph = ph; g.pw = pw;
+  g.To = (Ti + 2 * pt - kt) / st + 1;
+  g.Ho = (Hi + 2 * ph - kh) / sh + 1;
+  g.Wo = (Wi + 2 * pw - kw) / sw + 1;
+  return g;
+}
+
+static int num_sms = 148;
+
+// returns true on pass
+static bool run_case(const Case& c, int perf_iters) {
+  const ConvGeom& g = c.g;
+  const int B = c.B;
+  const int cp = pad16(g.cin), np = g.cout_pad();
+  const size_t in_pos = (size_t)B * g.Ti * g.Hi * g.Wi, out_pos = (size_t)B * g.To * g.Ho * g.Wo;
+
+  std::vector<float> x((size_t)in_pos * g.cin), w((size_t)g.cout * g.cin * g.kt * g.kh * g.kw);
+  std::vector<float> scale(np, 0.f), shift(np, 0.f), res;
+  for (auto& v : x) v = bf16_round(frand());
+  const float wamp = 1.f / sqrtf((float)(g.cin * g.kt * g.kh * g.kw));
+  for (auto& v : w) v = bf16_round(frand() * wamp * 1.7f);
+  for (int n = 0; n < g.cout; ++n) {
+    scale[n] = 0.75f + 0.5f * fabsf(frand());
+    shift[n] = 0.2f * frand();
+  }
+  if (c.residual) {
+    res.resize(out_pos * g.cout);
+    for (auto& v : res) v = bf16_round(frand());
+  }
+  // padded bf16 copies
+  std::vector<uint16_t> xb((size_t)in_pos * cp, 0), rb;
+  for (size_t i = 0; i < in_pos; ++i)
+    for (int ch = 0; ch < g.cin; ++ch) xb[i * cp + ch] = f32_to_bf16_bits(x[i * g.cin + ch]);
+  if (c.residual) {
+    rb.assign(out_pos * np, 0);
+    for (size_t i = 0; i < out_pos; ++i)
+      for (int ch = 0; ch < g.cout; ++ch) rb[i * np + ch] = f32_to_bf16_bits(res[i * g.cout + ch]);
+  }
+  std::vector<uint16_t> wp;
+  pack_conv_weights_tc(g, w.data(), &wp);
+  std::vector<float> wr;
+  pack_conv_weights_ref(g, w.data(), &wr);
+
+  float *dx, *dw, *dscale, *dshift, *dres = nullptr, *dy;
+  __nv_bfloat16 *dxb, *dwp, *drb = nullptr, *dyb;
+  CK(cudaMalloc(&dx, x.size() * 4));
+  CK(cudaMalloc(&dw, wr.size() * 4));
+  CK(cudaMalloc(&dscale, np * 4));
+  CK(cudaMalloc(&dshift, np * 4));
+  CK(cudaMalloc(&dy, out_pos * g.cout * 4));
+  CK(cudaMalloc(&dxb, xb.size() * 2));
+  CK(cudaMalloc(&dwp, wp.size() * 2));
+  CK(cudaMalloc(&dyb, out_pos * np * 2));
+  CK(cudaMemcpy(dx, x.data(), x.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dw, wr.data(), wr.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dscale, scale.data(), np * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dshift, shift.data(), np * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dxb, xb.data(), xb.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dwp, wp.data(), wp.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemset(dyb, 0xff, out_pos * np * 2));
+  if (c.residual) {
+    CK(cudaMalloc(&dres, res.size() * 4));
+    CK(cudaMalloc(&drb, rb.size() * 2));
+    CK(cudaMemcpy(dres, res.data(), res.size() * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(drb, rb.data(), rb.size() * 2, cudaMemcpyHostToDevice));
+  }
+
+  ConvRefParams rp;
+  rp.x = dx; rp.w = dw; rp.scale = dscale; rp.shift = dshift; rp.residual = dres; rp.y = dy;
+  rp.B = B; rp.Ti = g.Ti; rp.Hi = g.Hi; rp.Wi = g.Wi; rp.Cin = g.cin;
+  rp.To = g.To; rp.Ho = g.Ho; rp.Wo = g.Wo; rp.Cout = g.cout;
+  rp.kt = g.kt; rp.kh = g.kh; rp.kw = g.kw; rp.st = g.st; rp.sh = g.sh; rp.sw = g.sw;
+  rp.pt = g.pt; rp.ph = g.ph; rp.pw = g.pw; rp.relu = c.relu;
+  CK(launch_conv_ref(rp, 0));
+
+  ConvTcParams tp;
+  std::string err;
+  if (!build_conv_tc_params(g, B, dxb, dwp, dyb, dscale, dshift, drb, c.relu, num_sms, &tp, &err)) {
+    printf("%-28s PLAN FAILED: %s\n", c.name, err.c_str());
+    return false;
+  }
+  CK(launch_conv_tc(tp, num_sms, 0));
+  CK(cudaDeviceSynchronize());
+
+  std::vector<float> yr(out_pos * g.cout);
+  std::vector<uint16_t> yb(out_pos * np);
+  CK(cudaMemcpy(yr.data(), dy, yr.size() * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(yb.data(), dyb, yb.size() * 2, cudaMemcpyDeviceToHost));
+  double max_ref = 0, max_err = 0;
+  size_t bad_pad = 0, worst = 0;
+  for (size_t i = 0; i < out_pos; ++i) {
+    for (int ch = 0; ch < np; ++ch) {
+      const float t = bf16_bits_to_f32(yb[i * np + ch]);
+      if (ch >= g.cout) {
+        if (t != 0.f) ++bad_pad;
+        continue;
+      }
+      const float r = yr[i * g.cout + ch];
+      if (fabs(r) > max_ref) max_ref = fabs(r);
+      const double e = fabs((double)t - r);
+      if (!(e <= max_err)) {  // also catches NaN
+        max_err = e;
+        worst = i * np + ch;
+      }
+    }
+  }
+  const double rel = max_err / (max_ref > 0 ? max_ref : 1);
+  const bool pass = rel < 1e-2 && bad_pad == 0;
+  const int bw = 1 << tp.lbw, bh = 1 << tp.lbh, bt = 1 << tp.lbt;
+  printf("%-28s B=%-2d box(w%d h%d t%d b%d) N=%dx%d stages=%d taps=%d  max|ref|=%.3f max|err|=%.4f "
+         "rel=%.2e pad_bad=%zu worst@%zu  %s\n",
+         c.name, B, bw, bh, bt, 128 / (bw * bh * bt), tp.n_tiles, tp.block_n, tp.num_stages,
+         tp.num_taps, max_ref, max_err, rel, bad_pad, worst, pass ? "PASS" : "FAIL");
+
+  if (perf_iters > 0 && pass) {
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    for (int i = 0; i < 3; ++i) CK(launch_conv_tc(tp, num_sms, 0));
+    CK(cudaEventRecord(e0));
+    for (int i = 0; i < perf_iters; ++i) CK(launch_conv_tc(tp, num_sms, 0));
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    float ms;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    const double us = ms * 1e3 / perf_iters;
+    const double bytes = (double)g.in_elems(B) * 2 + g.out_elems(B) * 2 * (c.residual ? 2 : 1) +
+                         (double)wp.size() * 2;
+    printf("    perf: %.1f us  %.1f TFLOP/s (real-channel flops)  %.0f GB/s (min traffic)\n", us,
+           g.flops(B) / us * 1e-6, bytes / us * 1e-3);
+  }
+  cudaFree(dx); cudaFree(dw); cudaFree(dscale); cudaFree(dshift); cudaFree(dy); cudaFree(dxb);
+  cudaFree(dwp); cudaFree(dyb);
+  if (dres) cudaFree(dres);
+  if (drb) cudaFree(drb);
+  return pass;
+}
+
+// stem: uint8 frames -> unfolded rows -> tcgen05, against uint8 -> fp32 NDHWC -> direct conv
+static bool run_stem(int B) {
+  ConvGeom g = geom(8, 112, 112, 3, 83, 1, 7, 7, 1, 2, 2, 0, 3, 3);
+  ConvGeom gu = g;
+  gu.stem_unfolded = true;
+  const int np = g.cout_pad();
+  const size_t in_bytes = (size_t)B * 8 * 3 * 112 * 112, out_pos = (size_t)B * g.To * g.Ho * g.Wo;
+  std::vector<uint8_t> frames(in_bytes);
+  for (auto& v : frames) {
+    rng_state = rng_state * 1664525u + 1013904223u;
+    v = (uint8_t)(rng_state >> 24);
+  }
+  std::vector<float> w((size_t)g.cout * 3 * 49), scale(np, 0.f), shift(np, 0.f);
+  for (auto& v : w) v = bf16_round(frand() * 0.02f);
+  for (int n = 0; n < g.cout; ++n) {
+    scale[n] = 0.75f + 0.5f * fabsf(frand());
+    shift[n] = 0.2f * frand();
+  }
+  std::vector<uint16_t> wp;
+  pack_conv_weights_tc(gu, w.data(), &wp);
+  std::vector<float> wr;
+  pack_conv_weights_ref(g, w.data(), &wr);
+  uint8_t* dframes;
+  float *dxf, *dw, *dscale, *dshift, *dy;
+  __nv_bfloat16 *du, *dwp, *dyb;
+  CK(cudaMalloc(&dframes, in_bytes));
+  CK(cudaMalloc(&dxf, in_bytes * 4));
+  CK(cudaMalloc(&dw, wr.size() * 4));
+  CK(cudaMalloc(&dscale, np * 4));
+  CK(cudaMalloc(&dshift, np * 4));
+  CK(cudaMalloc(&dy, out_pos * g.cout * 4));
+  CK(cudaMalloc(&du, (size_t)gu.in_elems(B) * 2));
+  CK(cudaMalloc(&dwp, wp.size() * 2));
+  CK(cudaMalloc(&dyb, out_pos * np * 2));
+  CK(cudaMemcpy(dframes, frames.data(), in_bytes, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dw, wr.data(), wr.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dscale, scale.data(), np * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dshift, shift.data(), np * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dwp, wp.data(), wp.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemset(dyb, 0xff, out_pos * np * 2));
+  CK(launch_pre_u8_to_f32_ndhwc(dframes, B, nullptr, nullptr, dxf, 0));
+  CK(launch_pre_u8_to_stem(dframes, B, nullptr, nullptr, du, 0));
+  ConvRefParams rp;
+  rp.x = dxf; rp.w = dw; rp.scale = dscale; rp.shift = dshift; rp.residual = nullptr; rp.y = dy;
+  rp.B = B; rp.Ti = 8; rp.Hi = 112; rp.Wi = 112; rp.Cin = 3;
+  rp.To = g.To; rp.Ho = g.Ho; rp.Wo = g.Wo; rp.Cout = g.cout;
+  rp.kt = 1; rp.kh = 7; rp.kw = 7; rp.st = 1; rp.sh = 2; rp.sw = 2; rp.pt = 0; rp.ph = 3; rp.pw = 3;
+  rp.relu = 1;
+  CK(launch_conv_ref(rp, 0));
+  ConvTcParams tp;
+  std::string err;
+  if (!build_conv_tc_params(gu, B, du, dwp, dyb, dscale, dshift, nullptr, true, num_sms, &tp, &err)) {
+    printf("stem spatial PLAN FAILED: %s\n", err.c_str());
+    return false;
+  }
+  CK(launch_conv_tc(tp, num_sms, 0));
+  CK(cudaDeviceSynchronize());
+  std::vector<float> yr(out_pos * g.cout);
+  std::vector<uint16_t> yb(out_pos * np);
+  CK(cudaMemcpy(yr.data(), dy, yr.size() * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(yb.data(), dyb, yb.size() * 2, cudaMemcpyDeviceToHost));
+  double max_ref = 0, max_err = 0;
+  size_t bad_pad = 0;
+  for (size_t i = 0; i < out_pos; ++i)
+    for (int ch = 0; ch < np; ++ch) {
+      const float t = bf16_bits_to_f32(yb[i * np + ch]);
+      if (ch >= g.cout) {
+        if (t != 0.f) ++bad_pad;
+        continue;
+      }
+      const float r = yr[i * g.cout + ch];
+      if (fabs(r) > max_ref) max_ref = fabs(r);
+      const double e = fabs((double)t - r);
+      if (!(e <= max_err)) max_err = e;
+    }
+  const double rel = max_err / (max_ref > 0 ? max_ref : 1);
+  const bool pass = rel < 1e-2 && bad_pad == 0;
+  printf("%-28s B=%-2d N=%dx%d stages=%d taps=%d  max|ref|=%.3f max|err|=%.4f rel=%.2e pad_bad=%zu  %s\n",
+         "stem spatial (unfolded)", B, tp.n_tiles, tp.block_n, tp.num_stages, tp.num_taps, max_ref,
+         max_err, rel, bad_pad, pass ? "PASS" : "FAIL");
+  cudaFree(dframes); cudaFree(dxf); cudaFree(dw); cudaFree(dscale); cudaFree(dshift); cudaFree(dy);
+  cudaFree(du); cudaFree(dwp); cudaFree(dyb);
+  return pass;
+}
+
+int main(int argc, char** argv) {
+  const int perf_batch = argc > 1 ? atoi(argv[1]) : 0;
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, 0));
+  num_sms = prop.multiProcessorCount;
+  printf("device: %s, %d SMs, cc %d.%d\n", prop.name, num_sms, prop.major, prop.minor);
+
+  std::vector<Case> cases = {
+      {"tiny 1x1x1 64->64", geom(2, 8, 8, 64, 64, 1, 1, 1, 1, 1, 1, 0, 0, 0), 1, false, false},
+      {"tiny 1x3x3 64->64", geom(2, 8, 8, 64, 64, 1, 3, 3, 1, 1, 1, 0, 1, 1), 1, false, false},
+      {"conv2 spatial 64->144", geom(8, 56, 56, 64, 144, 1, 3, 3, 1, 1, 1, 0, 1, 1), 2, true, false},
+      {"conv2 temporal 144->64 +res", geom(8, 56, 56, 144, 64, 3, 1, 1, 1, 1, 1, 1, 0, 0), 2, true, true},
+      {"conv3b1 spatial s2 64->230", geom(8, 56, 56, 64, 230, 1, 3, 3, 1, 2, 2, 0, 1, 1), 2, true, false},
+      {"conv3b1 temporal s2 230->128", geom(8, 28, 28, 230, 128, 3, 1, 1, 2, 1, 1, 1, 0, 0), 2, true, false},
+      {"short3 spatial k1s2 64->42", geom(8, 56, 56, 64, 42, 1, 1, 1, 1, 2, 2, 0, 0, 0), 2, true, false},
+      {"short3 temporal k1s2 42->128", geom(8, 28, 28, 42, 128, 1, 1, 1, 2, 1, 1, 0, 0, 0), 2, false, false},
+      {"conv3 spatial 128->288", geom(4, 28, 28, 128, 288, 1, 3, 3, 1, 1, 1, 0, 1, 1), 3, true, false},
+      {"conv4 spatial 256->576", geom(2, 14, 14, 256, 576, 1, 3, 3, 1, 1, 1, 0, 1, 1), 3, true, false},
+      {"conv4 temporal 576->256 +res", geom(2, 14, 14, 576, 256, 3, 1, 1, 1, 1, 1, 1, 0, 0), 3, true, true},
+      {"conv5b1 spatial s2 256->921", geom(2, 14, 14, 256, 921, 1, 3, 3, 1, 2, 2, 0, 1, 1), 3, true, false},
+      {"conv5 spatial 512->1152", geom(1, 7, 7, 512, 1152, 1, 3, 3, 1, 1, 1, 0, 1, 1), 3, true, false},
+      {"conv5 temporal 1152->512 +res", geom(1, 7, 7, 1152, 512, 3, 1, 1, 1, 1, 1, 1, 0, 0), 3, true, true},
+      {"stem temporal 83->64", geom(8, 56, 56, 83, 64, 3, 1, 1, 1, 1, 1, 1, 0, 0), 1, false, false},
+  };
+  int failed = 0;
+  for (const Case& c : cases) failed += run_case(c, 0) ? 0 : 1;
+  failed += run_stem(2) ? 0 : 1;
+
+  if (perf_batch > 0 && failed == 0) {
+    printf("---- perf at B=%d\n", perf_batch);
+    for (Case c : cases) {
+      if (c.g.Hi < 7 || c.g.Hi == 8) continue;
+      c.B = perf_batch;
+      run_case(c, 20);
+    }
+  }
+  printf("%s (%d failed)\n", failed ? "SOME TESTS FAILED" : "ALL TESTS PASSED", failed);
+  return failed ? 1 : 0;
+}
