@@ -1,0 +1,113 @@
+/* rnb_b200 -- C ABI of the B200-native R(2+1)D hot path of the RnB video-inference benchmark.
+ *
+ * Every entry point takes plain pointers and sizes (no torch types), returns 0 on success or a
+ * negative RNB_E* code, never throws, and is asynchronous with respect to the CUDA stream it is
+ * given: the caller synchronises, exactly as RnB's runner does after calling a step
+ * (reference runner.py:125-128).  `stream` is a cudaStream_t passed as void*; pass the stream the
+ * runner made current (reference runner.py:41-45), never rely on the legacy default stream.
+ * rnb_last_error() returns a human-readable message for the calling thread's last failure.
+ *
+ * File:line citations below are into the reference tree (snuspl/rnb @ 938d079) and name the
+ * reference code each entry point replaces.
+ */
+#ifndef RNB_B200_H_
+#define RNB_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RNB_OK 0
+#define RNB_EINVAL (-1)   /* bad argument / unsupported configuration        */
+#define RNB_ECUDA (-2)    /* a CUDA runtime or driver call failed             */
+#define RNB_EPARAM (-3)   /* a state_dict entry is missing or has a bad shape */
+#define RNB_ESTATE (-4)   /* call order violated (e.g. forward before finalize) */
+
+/* arithmetic mode of a model handle */
+#define RNB_DTYPE_F32 0   /* fp32 direct convolutions (parity mode)                     */
+#define RNB_DTYPE_BF16 1  /* bf16 operands, fp32 accumulation on tcgen05 tensor cores   */
+
+/* tensor formats at the boundary */
+#define RNB_FMT_U8_NTCHW 0    /* uint8 (B, 8, 3, 112, 112): loader frames, models/r2p1d/model.py:140-147 */
+#define RNB_FMT_F32_NCDHW 1   /* fp32 (B, C, T, H, W): RnB's inter-step tensors, control.py:41            */
+#define RNB_FMT_BF16_NDHWC 2  /* bf16 (B, T, H, W, pad16(C)): this library's private hand-off format      */
+#define RNB_FMT_F32_LOGITS 3  /* fp32 (B, num_classes): only as the output of a model ending at layer 5  */
+
+/* Select `device` for the calling thread and check that it is an sm_100 GPU.
+ * Replaces torch.cuda.set_device(g_idx) at runner.py:31-32 for code that does not go through torch. */
+int rnb_init(int device);
+
+/* Build layers start_idx..end_idx (1 = stem ... 5 = conv5 + pool + classifier) of R(2+1)D on the
+ * current device.  `layer_sizes` has one entry per layer of the range, stem position included and
+ * ignored -- the indexing rule of R2Plus1DLayerNet (models/r2p1d/network.py:18-34) as driven by
+ * R2P1DRunner (models/r2p1d/model.py:35-49); NULL means two blocks per stage (model.py:46-47).
+ * Replaces R2Plus1DLayerWrapper(...).to(device) at models/r2p1d/model.py:49 and
+ * R2Plus1DClassifier(...) at model.py:177. */
+int rnb_r2p1d_create(const int* layer_sizes, int n_layer_sizes, int start_idx, int end_idx,
+                     int num_classes, int dtype, int max_batch, void** out_handle);
+
+/* Hand over one state_dict entry (host fp32, torch layout) under its reference key, e.g.
+ * "res2plus1d.conv2.block1.conv1.spatial_conv.weight" or "linear.bias".  Keys outside the layer
+ * range and "num_batches_tracked" entries are accepted and ignored, so the prefix filter of
+ * models/r2p1d/model.py:52-63 is not needed.  Replaces model.load_state_dict at model.py:63,182. */
+int rnb_r2p1d_load_param(void* handle, const char* key, const float* host_data, const int64_t* shape,
+                         int ndim);
+
+/* Fold BatchNorm (inference statistics) and biases into per-channel scale/shift, repack the
+ * weights for the tensor cores, upload everything and allocate the activation arena.  After this
+ * call the handle never allocates again except when it first sees a new batch size. */
+int rnb_r2p1d_finalize(void* handle);
+
+/* One forward pass over `batch` clips.  `in`/`out` are device pointers.
+ *   in_fmt : U8_NTCHW (only when start_idx == 1; fuses the loader's float()+permute of
+ *            models/r2p1d/model.py:149-150), F32_NCDHW (shape of model.py:29-33) or BF16_NDHWC.
+ *   out_fmt: F32_LOGITS when end_idx == 5, else F32_NCDHW or BF16_NDHWC.
+ * Replaces self.model(tensor) at models/r2p1d/model.py:84 and model.py:228. */
+int rnb_r2p1d_forward(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
+                      void* stream);
+
+/* Per-clip logical shape (C, T, H, W) of the handle's input (which = 0) or output (which = 1);
+ * for a model ending at layer 5 the output is (num_classes, 1, 1, 1).  Mirrors
+ * R2P1DRunner.input_dict at models/r2p1d/model.py:29-33. */
+int rnb_r2p1d_io_shape(void* handle, int which, int64_t shape4[4]);
+
+/* Bookkeeping for benchmarks: algorithmic FLOPs of one forward over `batch` clips (2 x MACs of
+ * every convolution and the classifier) and the number of kernels one forward launches. */
+double rnb_r2p1d_flops(void* handle, int batch);
+int rnb_r2p1d_num_launches(void* handle);
+
+void rnb_r2p1d_destroy(void* handle);
+
+/* uint8 loader frames (B, 8, 3, 112, 112) -> value * scale[c] + bias[c] in `out_fmt`
+ * (F32_NCDHW = exactly frames.float().permute(0, 2, 1, 3, 4) made contiguous, which the reference
+ * does at models/r2p1d/model.py:149-150 plus the strided copy at runner.py:167-170; or
+ * BF16_NDHWC with 16 channel slots).  scale3/bias3 are HOST arrays of 3 floats or NULL (identity,
+ * the reference behaviour). */
+int rnb_preprocess_u8(const uint8_t* in, int batch, const float* scale3, const float* bias3,
+                      void* out, int out_fmt, void* stream);
+
+/* Concatenate k row-blocks (rows[i] rows of row_bytes bytes each, device pointers in the HOST
+ * array srcs) into dst.  Replaces torch.cat(self.stacked_tensors, dim=0) at batcher.py:28. */
+int rnb_batch_gather(const void* const* srcs, const int* rows, int k, void* dst, size_t row_bytes,
+                     void* stream);
+
+/* sum[j] = sum over rows of logits[r][j] (optional, may be NULL) and cls = argmax_j sum[j], lowest
+ * index on ties.  Replaces tensor.cpu().numpy().sum(axis=0) / .argmax() at
+ * models/r2p1d/model.py:254,259,278. */
+int rnb_logits_sum_argmax(const float* logits, int rows, int classes, float* sum, int* cls,
+                          void* stream);
+
+/* Copy `bytes` from src on device src_dev to dst on device dst_dev (NVLink peer copy when they
+ * differ), ordered on `stream`.  Replaces placeholder[:n].copy_(shared[:n]) at runner.py:112-113
+ * and shared[:n].copy_(segment) at runner.py:170. */
+int rnb_peer_copy(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes, void* stream);
+
+const char* rnb_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RNB_B200_H_ */

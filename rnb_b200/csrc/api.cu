@@ -1,0 +1,179 @@
+// extern "C" surface of librnb_b200.so (declared in include/rnb_b200.h).
+#include <string>
+#include <vector>
+
+#include "../../include/rnb_b200.h"
+#include "kernels.cuh"
+#include "model.cuh"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+  g_last_error = msg;
+  return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  (void)cudaGetLastError();
+  return fail(RNB_ECUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rnb_last_error(void) { return g_last_error.c_str(); }
+
+int rnb_init(int device) {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+  if (device < 0 || device >= count)
+    return fail(RNB_EINVAL, "device " + std::to_string(device) + " out of range (" +
+                                std::to_string(count) + " visible)");
+  e = cudaSetDevice(device);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+  int major = 0;
+  e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
+  if (major != 10)
+    return fail(RNB_EINVAL, "rnb_b200 is built for sm_100a only; device " + std::to_string(device) +
+                                " has compute capability major " + std::to_string(major));
+  return RNB_OK;
+}
+
+int rnb_r2p1d_create(const int* layer_sizes, int n_layer_sizes, int start_idx, int end_idx,
+                     int num_classes, int dtype, int max_batch, void** out_handle) {
+  if (!out_handle) return fail(RNB_EINVAL, "out_handle is NULL");
+  *out_handle = nullptr;
+  // same range check as R2P1DRunner.__init__ (models/r2p1d/model.py:38-44)
+  if (start_idx < 1) return fail(RNB_EINVAL, "start_index must be >= 1");
+  if (end_idx > 5) return fail(RNB_EINVAL, "end_index must be <= 5");
+  if (start_idx > end_idx) return fail(RNB_EINVAL, "start_index must be <= end_index");
+  if (dtype != RNB_DTYPE_F32 && dtype != RNB_DTYPE_BF16) return fail(RNB_EINVAL, "unknown dtype");
+  if (max_batch < 1) return fail(RNB_EINVAL, "max_batch must be >= 1");
+  if (num_classes < 1) return fail(RNB_EINVAL, "num_classes must be >= 1");
+  std::vector<int> ls;
+  if (layer_sizes) {
+    if (n_layer_sizes != end_idx - start_idx + 1)
+      return fail(RNB_EINVAL, "layer_sizes needs one entry per layer of the range (stem included)");
+    ls.assign(layer_sizes, layer_sizes + n_layer_sizes);
+  }
+  *out_handle = new rnb::R2P1DModel(ls, start_idx, end_idx, num_classes, dtype, max_batch);
+  return RNB_OK;
+}
+
+int rnb_r2p1d_load_param(void* handle, const char* key, const float* host_data, const int64_t* shape,
+                         int ndim) {
+  if (!handle || !key || !host_data || (ndim > 0 && !shape) || ndim < 0 || ndim > 8)
+    return fail(RNB_EINVAL, "bad argument to rnb_r2p1d_load_param");
+  std::string err;
+  if (!static_cast<rnb::R2P1DModel*>(handle)->load_param(key, host_data, shape, ndim, &err))
+    return fail(RNB_ESTATE, err);
+  return RNB_OK;
+}
+
+int rnb_r2p1d_finalize(void* handle) {
+  if (!handle) return fail(RNB_EINVAL, "handle is NULL");
+  std::string err;
+  const int rc = static_cast<rnb::R2P1DModel*>(handle)->finalize(&err);
+  if (rc != RNB_OK) {
+    (void)cudaGetLastError();
+    return fail(rc, err);
+  }
+  return RNB_OK;
+}
+
+int rnb_r2p1d_forward(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
+                      void* stream) {
+  if (!handle) return fail(RNB_EINVAL, "handle is NULL");
+  std::string err;
+  const int rc = static_cast<rnb::R2P1DModel*>(handle)->forward(
+      in, in_fmt, batch, out, out_fmt, static_cast<cudaStream_t>(stream), &err);
+  if (rc != RNB_OK) {
+    (void)cudaGetLastError();
+    return fail(rc, err);
+  }
+  return RNB_OK;
+}
+
+int rnb_r2p1d_io_shape(void* handle, int which, int64_t shape4[4]) {
+  if (!handle || !shape4 || (which != 0 && which != 1))
+    return fail(RNB_EINVAL, "bad argument to rnb_r2p1d_io_shape");
+  static_cast<rnb::R2P1DModel*>(handle)->io_shape(which, shape4);
+  return RNB_OK;
+}
+
+double rnb_r2p1d_flops(void* handle, int batch) {
+  auto* m = static_cast<rnb::R2P1DModel*>(handle);
+  if (!m || !m->finalized()) return 0.0;
+  return m->flops(batch);
+}
+
+int rnb_r2p1d_num_launches(void* handle) {
+  auto* m = static_cast<rnb::R2P1DModel*>(handle);
+  if (!m || !m->finalized()) return fail(RNB_ESTATE, "handle not finalized");
+  return m->num_launches();
+}
+
+void rnb_r2p1d_destroy(void* handle) { delete static_cast<rnb::R2P1DModel*>(handle); }
+
+int rnb_preprocess_u8(const uint8_t* in, int batch, const float* scale3, const float* bias3,
+                      void* out, int out_fmt, void* stream) {
+  if (batch < 0) return fail(RNB_EINVAL, "negative batch");
+  if (batch == 0) return RNB_OK;
+  if (!in || !out) return fail(RNB_EINVAL, "null pointer");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  cudaError_t e;
+  if (out_fmt == RNB_FMT_F32_NCDHW) {
+    e = rnb::launch_pre_u8_to_f32_ncdhw(in, batch, scale3, bias3, static_cast<float*>(out), s);
+  } else if (out_fmt == RNB_FMT_BF16_NDHWC) {
+    e = rnb::launch_pre_u8_to_bf16_ndhwc(in, batch, scale3, bias3,
+                                         static_cast<__nv_bfloat16*>(out), 16, s);
+  } else {
+    return fail(RNB_EINVAL, "rnb_preprocess_u8: out_fmt must be F32_NCDHW or BF16_NDHWC");
+  }
+  if (e != cudaSuccess) return cuda_fail(e, "rnb_preprocess_u8");
+  return RNB_OK;
+}
+
+int rnb_batch_gather(const void* const* srcs, const int* rows, int k, void* dst, size_t row_bytes,
+                     void* stream) {
+  if (k < 0 || k > rnb::kMaxGatherSrcs)
+    return fail(RNB_EINVAL, "rnb_batch_gather: k must be in [0, " +
+                                std::to_string(rnb::kMaxGatherSrcs) + "]");
+  if (k == 0) return RNB_OK;
+  if (!srcs || !rows || !dst) return fail(RNB_EINVAL, "null pointer");
+  for (int i = 0; i < k; ++i)
+    if (rows[i] < 0 || (rows[i] > 0 && !srcs[i]))
+      return fail(RNB_EINVAL, "rnb_batch_gather: bad source " + std::to_string(i));
+  cudaError_t e = rnb::launch_batch_gather(srcs, rows, k, dst, row_bytes,
+                                           static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return cuda_fail(e, "rnb_batch_gather");
+  return RNB_OK;
+}
+
+int rnb_logits_sum_argmax(const float* logits, int rows, int classes, float* sum, int* cls,
+                          void* stream) {
+  if (!logits || rows < 0 || classes < 1) return fail(RNB_EINVAL, "bad argument");
+  cudaError_t e = rnb::launch_logits_sum_argmax(logits, rows, classes, sum, cls,
+                                                static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return cuda_fail(e, "rnb_logits_sum_argmax");
+  return RNB_OK;
+}
+
+int rnb_peer_copy(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes,
+                  void* stream) {
+  if (bytes == 0) return RNB_OK;
+  if (!dst || !src) return fail(RNB_EINVAL, "null pointer");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  cudaError_t e = (dst_dev == src_dev)
+                      ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, s)
+                      : cudaMemcpyPeerAsync(dst, dst_dev, src, src_dev, bytes, s);
+  if (e != cudaSuccess) return cuda_fail(e, "rnb_peer_copy");
+  return RNB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,454 @@
+// R(2+1)D layer-range model on top of the convolution kernels.
+//
+// Structure follows the reference's R2Plus1DLayerNet / R2Plus1DLayerWrapper
+// (models/r2p1d/network.py:9-60) and the un-vendored irhum/R2Plus1D-PyTorch modules they
+// instantiate (see oracle/r2p1d_ref.py for what is pinned and what is assumed).  Every
+// SpatioTemporalConv becomes two convolution launches (1 x k x k, then k x 1 x 1) whose epilogues
+// carry the folded BatchNorm / bias, the ReLU and, for the second convolution of a residual block,
+// the shortcut add.
+#include "model.cuh"
+
+#include <math.h>
+#include <string.h>
+
+#include "../../include/rnb_b200.h"
+
+namespace rnb {
+
+namespace {
+constexpr float kBnEps = 1e-5f;  // torch.nn.BatchNorm3d default
+
+std::string shape_str(const std::vector<int64_t>& s) {
+  std::string r = "(";
+  for (size_t i = 0; i < s.size(); ++i) r += (i ? ", " : "") + std::to_string(s[i]);
+  return r + ")";
+}
+
+bool cuda_ok(cudaError_t e, const char* what, std::string* err) {
+  if (e == cudaSuccess) return true;
+  if (err) *err = std::string(what) + ": " + cudaGetErrorString(e);
+  return false;
+}
+
+int mid_channels(int cin, int cout, int kt, int kh, int kw) {
+  return (int)floor((double)(kt * kh * kw) * cin * cout / (double)(kh * kw * cin + kt * cout));
+}
+}  // namespace
+
+R2P1DModel::R2P1DModel(std::vector<int> layer_sizes, int start_idx, int end_idx, int num_classes,
+                       int dtype, int max_batch)
+    : layer_sizes_(std::move(layer_sizes)),
+      start_idx_(start_idx),
+      end_idx_(end_idx),
+      num_classes_(num_classes),
+      dtype_(dtype),
+      max_batch_(max_batch) {
+  static const Dims kIn[6] = {{}, {3, 8, 112, 112}, {64, 8, 56, 56}, {64, 8, 56, 56},
+                              {128, 4, 28, 28}, {256, 2, 14, 14}};
+  static const Dims kOut[6] = {{}, {64, 8, 56, 56}, {64, 8, 56, 56}, {128, 4, 28, 28},
+                               {256, 2, 14, 14}, {512, 1, 7, 7}};
+  in_dims_ = kIn[start_idx];
+  out_dims_ = kOut[end_idx];
+}
+
+R2P1DModel::~R2P1DModel() { release(); }
+
+void R2P1DModel::release() {
+  for (ConvOp& op : ops_) {
+    if (op.d_w) cudaFree(op.d_w);
+    if (op.d_scale) cudaFree(op.d_scale);
+    if (op.d_shift) cudaFree(op.d_shift);
+    op.d_w = nullptr;
+    op.d_scale = op.d_shift = nullptr;
+  }
+  for (void*& s : slots_) {
+    if (s) cudaFree(s);
+    s = nullptr;
+  }
+  if (d_fc_w_) cudaFree(d_fc_w_);
+  if (d_fc_b_) cudaFree(d_fc_b_);
+  d_fc_w_ = d_fc_b_ = nullptr;
+}
+
+bool R2P1DModel::load_param(const char* key, const float* data, const int64_t* shape, int ndim,
+                            std::string* err) {
+  if (finalized_) {
+    if (err) *err = "load_param after finalize";
+    return false;
+  }
+  HostTensor t;
+  int64_t n = 1;
+  for (int i = 0; i < ndim; ++i) {
+    t.shape.push_back(shape[i]);
+    n *= shape[i];
+  }
+  t.data.assign(data, data + n);
+  params_[key] = std::move(t);
+  return true;
+}
+
+const HostTensor* R2P1DModel::get(const std::string& key, std::vector<int64_t> shape,
+                                  std::string* err) const {
+  auto it = params_.find(key);
+  if (it == params_.end()) {
+    if (err) *err = "missing state_dict entry '" + key + "'";
+    return nullptr;
+  }
+  if (it->second.shape != shape) {
+    if (err)
+      *err = "state_dict entry '" + key + "' has shape " + shape_str(it->second.shape) +
+             ", expected " + shape_str(shape);
+    return nullptr;
+  }
+  return &it->second;
+}
+
+// y = gamma * (x + bias - mean) / sqrt(var + eps) + beta  ->  scale, shift applied to the raw conv
+bool R2P1DModel::fold_bn(const std::string& bn, const std::vector<float>& bias,
+                         std::vector<float>* scale, std::vector<float>* shift,
+                         std::string* err) const {
+  const int64_t n = (int64_t)bias.size();
+  scale->assign(n, 1.f);
+  *shift = bias;
+  if (bn.empty()) return true;
+  const HostTensor* gamma = get(bn + ".weight", {n}, err);
+  const HostTensor* beta = gamma ? get(bn + ".bias", {n}, err) : nullptr;
+  const HostTensor* mean = beta ? get(bn + ".running_mean", {n}, err) : nullptr;
+  const HostTensor* var = mean ? get(bn + ".running_var", {n}, err) : nullptr;
+  if (!var) return false;
+  for (int64_t i = 0; i < n; ++i) {
+    const float s = gamma->data[i] / sqrtf(var->data[i] + kBnEps);
+    (*scale)[i] = s;
+    (*shift)[i] = beta->data[i] + (bias[i] - mean->data[i]) * s;
+  }
+  return true;
+}
+
+bool R2P1DModel::add_st_conv(const std::string& prefix, int in_slot, int out_slot, Dims in, int cout,
+                             int kt, int kh, int kw, int st, int sh, int sw, int pt, int ph, int pw,
+                             const std::string& post_bn, bool relu, int res_slot, bool stem,
+                             Dims* out, std::string* err) {
+  const int mid = mid_channels(in.C, cout, kt, kh, kw);
+  // ---- spatial 1 x kh x kw, then the module's own BatchNorm + ReLU
+  ConvOp sp;
+  sp.name = prefix + ".spatial_conv";
+  sp.g.Ti = in.T; sp.g.Hi = in.H; sp.g.Wi = in.W; sp.g.cin = in.C; sp.g.cout = mid;
+  sp.g.kt = 1; sp.g.kh = kh; sp.g.kw = kw;
+  sp.g.st = 1; sp.g.sh = sh; sp.g.sw = sw;
+  sp.g.pt = 0; sp.g.ph = ph; sp.g.pw = pw;
+  sp.g.To = in.T;
+  sp.g.Ho = (in.H + 2 * ph - kh) / sh + 1;
+  sp.g.Wo = (in.W + 2 * pw - kw) / sw + 1;
+  sp.g.stem_unfolded = stem && dtype_ == RNB_DTYPE_BF16;
+  sp.in_slot = in_slot;
+  sp.out_slot = SLOT_M;
+  sp.relu = true;
+  const HostTensor* w = get(sp.name + ".weight", {mid, in.C, 1, kh, kw}, err);
+  const HostTensor* b = w ? get(sp.name + ".bias", {mid}, err) : nullptr;
+  if (!b) return false;
+  sp.w = w->data;
+  if (!fold_bn(prefix + ".bn", b->data, &sp.scale, &sp.shift, err)) return false;
+  // ---- temporal kt x 1 x 1, then whatever BatchNorm / ReLU / residual the caller attaches
+  ConvOp tp;
+  tp.name = prefix + ".temporal_conv";
+  tp.g.Ti = sp.g.To; tp.g.Hi = sp.g.Ho; tp.g.Wi = sp.g.Wo; tp.g.cin = mid; tp.g.cout = cout;
+  tp.g.kt = kt; tp.g.kh = 1; tp.g.kw = 1;
+  tp.g.st = st; tp.g.sh = 1; tp.g.sw = 1;
+  tp.g.pt = pt; tp.g.ph = 0; tp.g.pw = 0;
+  tp.g.To = (tp.g.Ti + 2 * pt - kt) / st + 1;
+  tp.g.Ho = tp.g.Hi;
+  tp.g.Wo = tp.g.Wi;
+  tp.in_slot = SLOT_M;
+  tp.out_slot = out_slot;
+  tp.res_slot = res_slot;
+  tp.relu = relu;
+  w = get(tp.name + ".weight", {cout, mid, kt, 1, 1}, err);
+  b = w ? get(tp.name + ".bias", {cout}, err) : nullptr;
+  if (!b) return false;
+  tp.w = w->data;
+  if (!fold_bn(post_bn, b->data, &tp.scale, &tp.shift, err)) return false;
+  *out = {cout, tp.g.To, tp.g.Ho, tp.g.Wo};
+  ops_.push_back(std::move(sp));
+  ops_.push_back(std::move(tp));
+  return true;
+}
+
+bool R2P1DModel::build_ops(std::string* err) {
+  ops_.clear();
+  int cur = SLOT_X, nxt = SLOT_Y;
+  Dims d = in_dims_;
+  static const int kStageOut[6] = {0, 64, 64, 128, 256, 512};
+  for (int layer = start_idx_, pos = 0; layer <= end_idx_; ++layer, ++pos) {
+    const std::string lp = "res2plus1d.conv" + std::to_string(layer);
+    if (layer == 1) {
+      // SpatioTemporalConv(3, 64, [3,7,7], stride=[1,2,2], padding=[1,3,3]); network.py:22.
+      // No BatchNorm / ReLU follows the stem (assumed from the public submodule).
+      if (!add_st_conv(lp, SLOT_U, cur, d, 64, 3, 7, 7, 1, 2, 2, 1, 3, 3, "", false, -1, true, &d,
+                       err))
+        return false;
+      continue;
+    }
+    const int n_blocks = layer_sizes_.empty() ? 2 : layer_sizes_[pos];
+    if (n_blocks < 1) {
+      if (err) *err = "layer_sizes entries of residual stages must be >= 1";
+      return false;
+    }
+    const bool down = layer >= 3;  // network.py:28,31,34
+    const int cout = kStageOut[layer];
+    for (int blk = 0; blk < n_blocks; ++blk) {
+      const std::string bp =
+          blk == 0 ? lp + ".block1" : lp + ".blocks." + std::to_string(blk - 1);
+      const bool ds = down && blk == 0;
+      int res = cur;
+      Dims dres = d, d1 = d, d2 = d;
+      if (ds) {
+        if (!add_st_conv(bp + ".downsampleconv", cur, SLOT_S, d, cout, 1, 1, 1, 2, 2, 2, 0, 0, 0,
+                         bp + ".downsamplebn", false, -1, false, &dres, err))
+          return false;
+        res = SLOT_S;
+      }
+      const int s = ds ? 2 : 1;
+      if (!add_st_conv(bp + ".conv1", cur, SLOT_R, d, cout, 3, 3, 3, s, s, s, 1, 1, 1, bp + ".bn1",
+                       true, -1, false, &d1, err))
+        return false;
+      if (!add_st_conv(bp + ".conv2", SLOT_R, nxt, d1, cout, 3, 3, 3, 1, 1, 1, 1, 1, 1, bp + ".bn2",
+                       true, res, false, &d2, err))
+        return false;
+      d = d2;
+      std::swap(cur, nxt);
+    }
+  }
+  final_slot_ = cur;
+  if (d.C != out_dims_.C || d.T != out_dims_.T || d.H != out_dims_.H || d.W != out_dims_.W) {
+    if (err) *err = "internal: activation shape does not match the reference's shape table";
+    return false;
+  }
+  return true;
+}
+
+int R2P1DModel::finalize(std::string* err) {
+  if (finalized_) return RNB_OK;
+  if (!cuda_ok(cudaGetDevice(&device_), "cudaGetDevice", err)) return RNB_ECUDA;
+  if (!cuda_ok(cudaDeviceGetAttribute(&num_sms_, cudaDevAttrMultiProcessorCount, device_),
+               "cudaDeviceGetAttribute", err))
+    return RNB_ECUDA;
+  if (!build_ops(err)) return RNB_EPARAM;
+
+  // ---- arena: every slot sized for its largest tenant at max_batch
+  memset(slot_elems_per_clip_, 0, sizeof slot_elems_per_clip_);
+  auto need = [&](int slot, size_t elems) {
+    if (elems > slot_elems_per_clip_[slot]) slot_elems_per_clip_[slot] = elems;
+  };
+  if (start_idx_ == 1) {
+    need(SLOT_U, dtype_ == RNB_DTYPE_BF16 ? (size_t)kClipT * kClipH * (kClipW / 2) * kStemUnfold
+                                          : (size_t)kClipT * kClipH * kClipW * kClipC);
+  } else {
+    need(SLOT_X, (size_t)in_dims_.T * in_dims_.H * in_dims_.W * chan_pad(in_dims_.C));
+  }
+  for (const ConvOp& op : ops_)
+    need(op.out_slot, (size_t)op.g.To * op.g.Ho * op.g.Wo * chan_pad(op.g.cout));
+  for (int s = 0; s < NUM_SLOTS; ++s) {
+    if (!slot_elems_per_clip_[s]) continue;
+    const size_t bytes = slot_elems_per_clip_[s] * (size_t)max_batch_ * elem_size();
+    if (!cuda_ok(cudaMalloc(&slots_[s], bytes), "cudaMalloc(activation arena)", err)) {
+      release();
+      return RNB_ECUDA;
+    }
+  }
+
+  // ---- parameters
+  for (ConvOp& op : ops_) {
+    const int np = chan_pad(op.g.cout);
+    std::vector<float> sc(np, 0.f), sh(np, 0.f);
+    memcpy(sc.data(), op.scale.data(), op.scale.size() * 4);
+    memcpy(sh.data(), op.shift.data(), op.shift.size() * 4);
+    bool ok = cuda_ok(cudaMalloc(&op.d_scale, np * 4), "cudaMalloc", err) &&
+              cuda_ok(cudaMalloc(&op.d_shift, np * 4), "cudaMalloc", err) &&
+              cuda_ok(cudaMemcpy(op.d_scale, sc.data(), np * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err) &&
+              cuda_ok(cudaMemcpy(op.d_shift, sh.data(), np * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err);
+    if (ok && dtype_ == RNB_DTYPE_BF16) {
+      std::vector<uint16_t> packed;
+      pack_conv_weights_tc(op.g, op.w.data(), &packed);
+      ok = cuda_ok(cudaMalloc(&op.d_w, packed.size() * 2), "cudaMalloc(weights)", err) &&
+           cuda_ok(cudaMemcpy(op.d_w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice),
+                   "cudaMemcpy(weights)", err);
+    } else if (ok) {
+      std::vector<float> packed;
+      pack_conv_weights_ref(op.g, op.w.data(), &packed);
+      ok = cuda_ok(cudaMalloc(&op.d_w, packed.size() * 4), "cudaMalloc(weights)", err) &&
+           cuda_ok(cudaMemcpy(op.d_w, packed.data(), packed.size() * 4, cudaMemcpyHostToDevice),
+                   "cudaMemcpy(weights)", err);
+    }
+    if (!ok) {
+      release();
+      return RNB_ECUDA;
+    }
+    op.w.clear();
+    op.w.shrink_to_fit();
+  }
+  if (end_idx_ == 5) {
+    const HostTensor* w = get("linear.weight", {num_classes_, 512}, err);
+    const HostTensor* b = w ? get("linear.bias", {num_classes_}, err) : nullptr;
+    if (!b) {
+      release();
+      return RNB_EPARAM;
+    }
+    bool ok = cuda_ok(cudaMalloc(&d_fc_w_, w->data.size() * 4), "cudaMalloc", err) &&
+              cuda_ok(cudaMalloc(&d_fc_b_, b->data.size() * 4), "cudaMalloc", err) &&
+              cuda_ok(cudaMemcpy(d_fc_w_, w->data.data(), w->data.size() * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err) &&
+              cuda_ok(cudaMemcpy(d_fc_b_, b->data.data(), b->data.size() * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err);
+    if (!ok) {
+      release();
+      return RNB_ECUDA;
+    }
+  }
+  params_.clear();
+  finalized_ = true;
+  return RNB_OK;
+}
+
+void R2P1DModel::io_shape(int which, int64_t shape4[4]) const {
+  if (which == 1 && end_idx_ == 5) {
+    shape4[0] = num_classes_;
+    shape4[1] = shape4[2] = shape4[3] = 1;
+    return;
+  }
+  const Dims& d = which == 0 ? in_dims_ : out_dims_;
+  shape4[0] = d.C;
+  shape4[1] = d.T;
+  shape4[2] = d.H;
+  shape4[3] = d.W;
+}
+
+double R2P1DModel::flops(int batch) const {
+  double f = 0;
+  for (const ConvOp& op : ops_) f += op.g.flops(batch);
+  if (end_idx_ == 5) f += 2.0 * batch * 512 * num_classes_;
+  return f;
+}
+
+int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int out_fmt,
+                        cudaStream_t stream, std::string* err) {
+  if (!finalized_) {
+    if (err) *err = "forward before finalize";
+    return RNB_ESTATE;
+  }
+  if (batch < 0 || batch > max_batch_) {
+    if (err)
+      *err = "batch " + std::to_string(batch) + " outside [0, max_batch = " +
+             std::to_string(max_batch_) + "]";
+    return RNB_EINVAL;
+  }
+  if (batch == 0) return RNB_OK;
+  if (in == nullptr || out == nullptr) {
+    if (err) *err = "null input or output pointer";
+    return RNB_EINVAL;
+  }
+  const bool tc = dtype_ == RNB_DTYPE_BF16;
+  const int want_out = end_idx_ == 5 ? RNB_FMT_F32_LOGITS : out_fmt;
+  if (out_fmt != want_out ||
+      (end_idx_ != 5 && out_fmt != RNB_FMT_F32_NCDHW && !(tc && out_fmt == RNB_FMT_BF16_NDHWC))) {
+    if (err) *err = "unsupported output format " + std::to_string(out_fmt) + " for this handle";
+    return RNB_EINVAL;
+  }
+  cudaError_t e = cudaSuccess;
+
+  // ---- stage the input into the arena
+  const int S_in = in_dims_.T * in_dims_.H * in_dims_.W;
+  if (start_idx_ == 1) {
+    if (in_fmt == RNB_FMT_U8_NTCHW) {
+      e = tc ? launch_pre_u8_to_stem((const uint8_t*)in, batch, nullptr, nullptr,
+                                     (__nv_bfloat16*)slots_[SLOT_U], stream)
+             : launch_pre_u8_to_f32_ndhwc((const uint8_t*)in, batch, nullptr, nullptr,
+                                          (float*)slots_[SLOT_U], stream);
+    } else if (in_fmt == RNB_FMT_F32_NCDHW) {
+      e = tc ? launch_f32_ncdhw_to_stem((const float*)in, batch, (__nv_bfloat16*)slots_[SLOT_U],
+                                        stream)
+             : launch_ncdhw_f32_to_ndhwc_f32((const float*)in, batch, kClipC, S_in,
+                                             (float*)slots_[SLOT_U], stream);
+    } else {
+      if (err) *err = "a model starting at layer 1 takes U8_NTCHW or F32_NCDHW input";
+      return RNB_EINVAL;
+    }
+  } else {
+    if (in_fmt == RNB_FMT_F32_NCDHW) {
+      e = tc ? launch_ncdhw_f32_to_ndhwc_bf16((const float*)in, batch, in_dims_.C, S_in,
+                                              pad16(in_dims_.C), (__nv_bfloat16*)slots_[SLOT_X],
+                                              stream)
+             : launch_ncdhw_f32_to_ndhwc_f32((const float*)in, batch, in_dims_.C, S_in,
+                                             (float*)slots_[SLOT_X], stream);
+    } else if (in_fmt == RNB_FMT_BF16_NDHWC && tc) {
+      e = cudaMemcpyAsync(slots_[SLOT_X], in, (size_t)batch * S_in * pad16(in_dims_.C) * 2,
+                          cudaMemcpyDeviceToDevice, stream);
+    } else {
+      if (err) *err = "unsupported input format " + std::to_string(in_fmt) + " for this handle";
+      return RNB_EINVAL;
+    }
+  }
+  if (!cuda_ok(e, "input staging", err)) return RNB_ECUDA;
+
+  // ---- convolutions
+  if (tc) {
+    auto it = plans_.find(batch);
+    if (it == plans_.end()) {
+      std::vector<ConvTcParams> plan(ops_.size());
+      for (size_t i = 0; i < ops_.size(); ++i) {
+        const ConvOp& op = ops_[i];
+        std::string perr;
+        if (!build_conv_tc_params(
+                op.g, batch, (const __nv_bfloat16*)slots_[op.in_slot],
+                (const __nv_bfloat16*)op.d_w, (__nv_bfloat16*)slots_[op.out_slot], op.d_scale,
+                op.d_shift,
+                op.res_slot >= 0 ? (const __nv_bfloat16*)slots_[op.res_slot] : nullptr, op.relu,
+                num_sms_, &plan[i], &perr)) {
+          if (err) *err = op.name + ": " + perr;
+          return RNB_ECUDA;
+        }
+      }
+      it = plans_.emplace(batch, std::move(plan)).first;
+    }
+    for (size_t i = 0; i < ops_.size(); ++i) {
+      if (!cuda_ok(launch_conv_tc(it->second[i], num_sms_, stream), ops_[i].name.c_str(), err))
+        return RNB_ECUDA;
+    }
+  } else {
+    for (const ConvOp& op : ops_) {
+      ConvRefParams rp;
+      rp.x = (const float*)slots_[op.in_slot];
+      rp.w = (const float*)op.d_w;
+      rp.scale = op.d_scale;
+      rp.shift = op.d_shift;
+      rp.residual = op.res_slot >= 0 ? (const float*)slots_[op.res_slot] : nullptr;
+      rp.y = (float*)slots_[op.out_slot];
+      rp.B = batch; rp.Ti = op.g.Ti; rp.Hi = op.g.Hi; rp.Wi = op.g.Wi; rp.Cin = op.g.cin;
+      rp.To = op.g.To; rp.Ho = op.g.Ho; rp.Wo = op.g.Wo; rp.Cout = op.g.cout;
+      rp.kt = op.g.kt; rp.kh = op.g.kh; rp.kw = op.g.kw;
+      rp.st = op.g.st; rp.sh = op.g.sh; rp.sw = op.g.sw;
+      rp.pt = op.g.pt; rp.ph = op.g.ph; rp.pw = op.g.pw;
+      rp.relu = op.relu ? 1 : 0;
+      if (!cuda_ok(launch_conv_ref(rp, stream), op.name.c_str(), err)) return RNB_ECUDA;
+    }
+  }
+
+  // ---- output
+  const int S_out = out_dims_.T * out_dims_.H * out_dims_.W;
+  if (end_idx_ == 5) {
+    e = tc ? launch_pool_fc_bf16((const __nv_bfloat16*)slots_[final_slot_], batch, S_out, 512,
+                                 d_fc_w_, d_fc_b_, num_classes_, (float*)out, stream)
+           : launch_pool_fc_f32((const float*)slots_[final_slot_], batch, S_out, 512, d_fc_w_,
+                                d_fc_b_, num_classes_, (float*)out, stream);
+  } else if (out_fmt == RNB_FMT_F32_NCDHW) {
+    e = tc ? launch_ndhwc_bf16_to_ncdhw_f32((const __nv_bfloat16*)slots_[final_slot_], batch,
+                                            out_dims_.C, S_out, pad16(out_dims_.C), (float*)out,
+                                            stream)
+           : launch_ndhwc_f32_to_ncdhw_f32((const float*)slots_[final_slot_], batch, out_dims_.C,
+                                           S_out, (float*)out, stream);
+  } else {
+    e = cudaMemcpyAsync(out, slots_[final_slot_], (size_t)batch * S_out * pad16(out_dims_.C) * 2,
+                        cudaMemcpyDeviceToDevice, stream);
+  }
+  if (!cuda_ok(e, "output stage", err)) return RNB_ECUDA;
+  return RNB_OK;
+}
+
+}  // namespace rnb

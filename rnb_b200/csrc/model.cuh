@@ -1,0 +1,81 @@
+// R(2+1)D layer-range model: op list, folded parameters, activation arena, per-batch launch plans.
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+#include "conv_tc.cuh"
+#include "kernels.cuh"
+#include "plan.cuh"
+
+namespace rnb {
+
+struct HostTensor {
+  std::vector<int64_t> shape;
+  std::vector<float> data;
+};
+
+// activation slots of the arena; every op reads one or two slots and writes a third
+enum Slot { SLOT_U = 0, SLOT_X, SLOT_M, SLOT_R, SLOT_S, SLOT_Y, NUM_SLOTS };
+
+struct ConvOp {
+  std::string name;  // state_dict prefix of the Conv3d, for error messages
+  ConvGeom g;
+  int in_slot = 0, out_slot = 0, res_slot = -1;
+  bool relu = false;
+  std::vector<float> w;             // torch layout (cout, cin, kt, kh, kw)
+  std::vector<float> scale, shift;  // folded BatchNorm + bias, length cout
+  // device copies
+  void* d_w = nullptr;  // bf16 K-major rows (tensor cores) or fp32 (kt,kh,kw,cin,cout)
+  float* d_scale = nullptr;
+  float* d_shift = nullptr;
+};
+
+class R2P1DModel {
+ public:
+  R2P1DModel(std::vector<int> layer_sizes, int start_idx, int end_idx, int num_classes, int dtype,
+             int max_batch);
+  ~R2P1DModel();
+
+  bool load_param(const char* key, const float* data, const int64_t* shape, int ndim,
+                  std::string* err);
+  int finalize(std::string* err);  // RNB_* code
+  int forward(const void* in, int in_fmt, int batch, void* out, int out_fmt, cudaStream_t stream,
+              std::string* err);
+  void io_shape(int which, int64_t shape4[4]) const;
+  double flops(int batch) const;
+  int num_launches() const { return (int)ops_.size() + 2; }
+  bool finalized() const { return finalized_; }
+
+ private:
+  struct Dims {
+    int C, T, H, W;
+  };
+  bool build_ops(std::string* err);
+  bool add_st_conv(const std::string& prefix, int in_slot, int out_slot, Dims in, int cout, int kt,
+                   int kh, int kw, int st, int sh, int sw, int pt, int ph, int pw,
+                   const std::string& post_bn, bool relu, int res_slot, bool stem, Dims* out,
+                   std::string* err);
+  const HostTensor* get(const std::string& key, std::vector<int64_t> shape, std::string* err) const;
+  bool fold_bn(const std::string& bn, const std::vector<float>& bias, std::vector<float>* scale,
+               std::vector<float>* shift, std::string* err) const;
+  size_t elem_size() const { return dtype_ == 1 ? 2 : 4; }
+  int chan_pad(int c) const { return dtype_ == 1 ? pad16(c) : c; }
+  void release();
+
+  std::vector<int> layer_sizes_;
+  int start_idx_, end_idx_, num_classes_, dtype_, max_batch_;
+  int device_ = 0, num_sms_ = 148;
+  bool finalized_ = false;
+  std::map<std::string, HostTensor> params_;
+  std::vector<ConvOp> ops_;
+  Dims in_dims_{}, out_dims_{};  // logical activation dims at the range boundaries
+  int final_slot_ = SLOT_X;
+  void* slots_[NUM_SLOTS] = {};
+  size_t slot_elems_per_clip_[NUM_SLOTS] = {};
+  float* d_fc_w_ = nullptr;
+  float* d_fc_b_ = nullptr;
+  std::map<int, std::vector<ConvTcParams>> plans_;  // tensor-core launch plans per batch size
+};
+
+}  // namespace rnb

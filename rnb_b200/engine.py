@@ -1,0 +1,211 @@
+"""Torch-facing wrapper of one ``rnb_r2p1d_*`` model handle.
+
+PyTorch is plumbing here (device memory, streams); every FLOP runs in ``librnb_b200.so``.
+"""
+import ctypes
+import math
+
+import torch
+
+from . import _lib
+
+NUM_CLASSES = 400
+# per-clip input shape by start layer and output shape by end layer
+# (reference models/r2p1d/model.py:29-33; the output of layer i is the input of layer i+1)
+LAYER_INPUT_SHAPE = {1: (3, 8, 112, 112), 2: (64, 8, 56, 56), 3: (64, 8, 56, 56),
+                     4: (128, 4, 28, 28), 5: (256, 2, 14, 14)}
+LAYER_OUTPUT_SHAPE = {1: (64, 8, 56, 56), 2: (64, 8, 56, 56), 3: (128, 4, 28, 28),
+                      4: (256, 2, 14, 14)}
+_STAGE = {2: (64, 64, False), 3: (64, 128, True), 4: (128, 256, True), 5: (256, 512, True)}
+
+
+def _mid(cin, cout, kt, kh, kw):
+    return int(math.floor((kt * kh * kw * cin * cout) / (kh * kw * cin + kt * cout)))
+
+
+def _st_conv_entries(prefix, cin, cout, k):
+    kt, kh, kw = k
+    mid = _mid(cin, cout, kt, kh, kw)
+    return [
+        (prefix + '.spatial_conv.weight', (mid, cin, 1, kh, kw)),
+        (prefix + '.spatial_conv.bias', (mid,)),
+        (prefix + '.bn.weight', (mid,)), (prefix + '.bn.bias', (mid,)),
+        (prefix + '.bn.running_mean', (mid,)), (prefix + '.bn.running_var', (mid,)),
+        (prefix + '.temporal_conv.weight', (cout, mid, kt, 1, 1)),
+        (prefix + '.temporal_conv.bias', (cout,)),
+    ]
+
+
+def _bn_entries(prefix, n):
+    return [(prefix + '.weight', (n,)), (prefix + '.bias', (n,)),
+            (prefix + '.running_mean', (n,)), (prefix + '.running_var', (n,))]
+
+
+def state_dict_spec(start_index=1, end_index=5, num_classes=NUM_CLASSES, layer_sizes=None):
+    """(key, shape) of every state_dict entry layers start..end need, in module order.
+
+    Key names are the reference's (``res2plus1d.conv{i}...``, ``linear``; reference
+    models/r2p1d/model.py:55-62), so a checkpoint trained on R2Plus1DClassifier loads unchanged.
+    """
+    if layer_sizes is None:
+        layer_sizes = [2] * (end_index - start_index + 1)
+    spec = []
+    for pos, layer in enumerate(range(start_index, end_index + 1)):
+        lp = 'res2plus1d.conv%d' % layer
+        if layer == 1:
+            spec += _st_conv_entries(lp, 3, 64, (3, 7, 7))
+            continue
+        cin, cout, down = _STAGE[layer]
+        for blk in range(layer_sizes[pos]):
+            bp = lp + ('.block1' if blk == 0 else '.blocks.%d' % (blk - 1))
+            ds = down and blk == 0
+            bcin = cin if blk == 0 else cout
+            if ds:
+                spec += _st_conv_entries(bp + '.downsampleconv', bcin, cout, (1, 1, 1))
+                spec += _bn_entries(bp + '.downsamplebn', cout)
+            spec += _st_conv_entries(bp + '.conv1', bcin, cout, (3, 3, 3))
+            spec += _bn_entries(bp + '.bn1', cout)
+            spec += _st_conv_entries(bp + '.conv2', cout, cout, (3, 3, 3))
+            spec += _bn_entries(bp + '.bn2', cout)
+    if end_index == 5:
+        spec += [('linear.weight', (num_classes, 512)), ('linear.bias', (num_classes,))]
+    return spec
+
+
+def random_state_dict(start_index=1, end_index=5, num_classes=NUM_CLASSES, layer_sizes=None,
+                      seed=0):
+    """Random-init weights with torch's default fan-in scaling (uniform +-1/sqrt(fan_in)).
+
+    Stands in for the reference's checkpoint (models/r2p1d/model.py:18,50), which is not
+    distributed; BatchNorm entries are identity statistics.
+    """
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+    for key, shape in state_dict_spec(start_index, end_index, num_classes, layer_sizes):
+        leaf = key.rsplit('.', 1)[1]
+        parent = key.rsplit('.', 2)[-2]
+        if parent.startswith('bn') or parent.endswith('bn'):
+            if leaf in ('weight', 'running_var'):
+                sd[key] = torch.ones(shape)
+            else:
+                sd[key] = torch.zeros(shape)
+        elif leaf == 'weight':
+            fan_in = 1
+            for d in shape[1:]:
+                fan_in *= d
+            bound = 1.0 / math.sqrt(fan_in)
+            sd[key] = (torch.rand(shape, generator=g) * 2 - 1) * bound
+            sd['_fan_in:' + key.rsplit('.', 1)[0]] = fan_in
+        else:
+            fan_in = sd.pop('_fan_in:' + key.rsplit('.', 1)[0])
+            bound = 1.0 / math.sqrt(fan_in)
+            sd[key] = (torch.rand(shape, generator=g) * 2 - 1) * bound
+    return sd
+
+
+class R2P1DEngine:
+    """Layers ``start_index..end_index`` of R(2+1)D on one GPU.
+
+    ``dtype`` is ``'bf16'`` (tensor cores, the fast path) or ``'fp32'`` (parity mode).
+    ``layer_sizes`` follows R2P1DRunner: one entry per layer of the range, stem position included
+    (reference models/r2p1d/model.py:46-47, network.py:20-34).
+    """
+
+    def __init__(self, device, state_dict, start_index=1, end_index=5, num_classes=NUM_CLASSES,
+                 layer_sizes=None, dtype='bf16', max_batch=64):
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+        if self.device.type != 'cuda':
+            raise RuntimeError('rnb_b200 runs on CUDA devices only (got %s)' % (self.device,))
+        self.start_index, self.end_index = start_index, end_index
+        self.num_classes = num_classes
+        self.dtype = dtype
+        self.max_batch = max_batch
+        dt = {'bf16': _lib.DTYPE_BF16, 'fp32': _lib.DTYPE_F32}[dtype]
+        index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device_index = index
+        self._handle = ctypes.c_void_p()
+        with torch.cuda.device(index):
+            _lib.check(self.lib.rnb_init(index))
+            if layer_sizes is not None:
+                arr = (ctypes.c_int * len(layer_sizes))(*[int(v) for v in layer_sizes])
+                n = len(layer_sizes)
+            else:
+                arr, n = None, 0
+            _lib.check(self.lib.rnb_r2p1d_create(arr, n, start_index, end_index, num_classes, dt,
+                                                 max_batch, ctypes.byref(self._handle)))
+            try:
+                for key, value in state_dict.items():
+                    if not torch.is_tensor(value) or key.endswith('num_batches_tracked'):
+                        continue
+                    host = value.detach().to('cpu', torch.float32).contiguous()
+                    shape = (ctypes.c_int64 * max(host.dim(), 1))(*host.shape)
+                    _lib.check(self.lib.rnb_r2p1d_load_param(
+                        self._handle, key.encode(), ctypes.c_void_p(host.data_ptr()), shape,
+                        host.dim()))
+                _lib.check(self.lib.rnb_r2p1d_finalize(self._handle))
+            except Exception:
+                self.close()
+                raise
+        if end_index == 5:
+            self.out_shape = (num_classes,)
+        else:
+            self.out_shape = LAYER_OUTPUT_SHAPE[end_index]
+        self.in_shape = LAYER_INPUT_SHAPE[start_index]
+        self._out = torch.empty((max_batch,) + self.out_shape, dtype=torch.float32,
+                                device=self.device)
+
+    # ------------------------------------------------------------------ lifetime
+    def close(self):
+        if getattr(self, '_handle', None) is not None and self._handle.value:
+            self.lib.rnb_r2p1d_destroy(self._handle)
+            self._handle = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001 - interpreter shutdown
+            pass
+
+    # ------------------------------------------------------------------ bookkeeping
+    def flops(self, batch):
+        return float(self.lib.rnb_r2p1d_flops(self._handle, batch))
+
+    @property
+    def num_launches(self):
+        return int(self.lib.rnb_r2p1d_num_launches(self._handle))
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x, out=None):
+        """``x``: uint8 (B, 8, 3, 112, 112) loader frames (start layer 1 only) or fp32
+        (B, C, T, H, W).  Returns fp32 (B, num_classes) logits, or fp32 (B, C, T, H, W) activations
+        when the range ends before layer 5.  The result aliases an engine-owned buffer that the
+        next call overwrites, unless ``out`` is given.  Asynchronous on the current stream.
+        """
+        batch = int(x.shape[0])
+        if x.device != self.device and not (x.is_cuda and x.device.index == self.device_index):
+            raise ValueError('input lives on %s, engine on %s' % (x.device, self.device))
+        if x.dtype == torch.uint8:
+            if tuple(x.shape[1:]) != (8, 3, 112, 112):
+                raise ValueError('uint8 frames must be (B, 8, 3, 112, 112), got %s' % (tuple(x.shape),))
+            fmt = _lib.FMT_U8_NTCHW
+        elif x.dtype == torch.float32:
+            if tuple(x.shape[1:]) != self.in_shape:
+                raise ValueError('expected input (B, %s), got %s' % (self.in_shape, tuple(x.shape)))
+            fmt = _lib.FMT_F32_NCDHW
+        else:
+            raise TypeError('input must be uint8 frames or float32 activations, got %s' % x.dtype)
+        if not x.is_contiguous():
+            x = x.contiguous()
+        if out is None:
+            if batch > self.max_batch:
+                raise ValueError('batch %d exceeds max_batch %d' % (batch, self.max_batch))
+            out = self._out[:batch]
+        out_fmt = _lib.FMT_F32_LOGITS if self.end_index == 5 else _lib.FMT_F32_NCDHW
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self.lib.rnb_r2p1d_forward(self._handle, ctypes.c_void_p(x.data_ptr()), fmt,
+                                              batch, ctypes.c_void_p(out.data_ptr()), out_fmt,
+                                              ctypes.c_void_p(stream)))
+        return out
+
+    __call__ = forward
