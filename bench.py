@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""Throughput of the R(2+1)D hot path on B200: clips/s, roofline of the convolution kernel, an
+end-to-end number with host buffers, and the CPU oracle timed beside them.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch 16] [--model r18|r34]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...       # the CPU implementation of the same path
+
+A step is one forward pass over one batch of synthetic uint8 clips.  Default workload =
+BASELINE.json configs[1]: R(2+1)D-18, bf16, batch 16, one B200 (one replica per GPU for N > 1,
+weak scaling, no collective on the data path).  Rank 0 prints exactly one JSON line.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+LAYER_SIZES = {'r18': [2, 2, 2, 2, 2], 'r34': [2, 3, 4, 6, 3]}  # runner form: stem slot first
+GFLOP_PER_CLIP = {'r18': 42.172, 'r34': 76.853}
+METRIC = 'R(2+1)D clips/sec (8x112x112 clips)'
+CLIP_BYTES = 8 * 3 * 112 * 112
+FALLBACK_PEAK_TFLOPS = 1590.0  # /opt/skills/guides/B200_PROFILING.md, used only without MEASURED_PEAKS.json
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=20)
+    ap.add_argument('--batch', type=int, default=16)
+    ap.add_argument('--model', choices=sorted(LAYER_SIZES), default='r18')
+    ap.add_argument('--dtype', choices=['bf16', 'fp32'], default='bf16')
+    ap.add_argument('--impl', choices=['b200', 'reference'], default='b200')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--ref-clips', type=int, default=4,
+                    help='clips per step of the CPU reference arm (a bounded sample of the batch)')
+    ap.add_argument('--profile-table', default=None,
+                    help='write the per-kernel timing table (markdown) to this path')
+    return ap.parse_args()
+
+
+def base_config(args, world):
+    return {'workload': workload_name(args), 'batch': args.batch, 'clip': '3x8x112x112 uint8',
+            'weights': 'random-init (seed 0), BatchNorm folded (inference statistics)',
+            'parallelism': 'replica x%d, no collective' % world}
+
+
+def workload_name(args):
+    return 'R(2+1)D-%s %s batch=%d single B200 (r2p1d-whole.json, one replica%s)' % (
+        args.model[1:], args.dtype, args.batch, ' per GPU' if args.gpus > 1 else '')
+
+
+# ------------------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the bench runs."""
+    REASONS = {0x4: 'sw_power_cap', 0x8: 'hw_slowdown', 0x20: 'sw_thermal_slowdown',
+               0x40: 'hw_thermal_slowdown', 0x80: 'hw_power_brake_slowdown'}
+
+    def __init__(self, index, period=0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples = []  # (time, sm_mhz, reasons_bits)
+        self.max_mhz = None
+        self.ok = False
+        self._stop_flag = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self._stop_flag.is_set():
+            try:
+                mhz = int(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+                try:
+                    bits = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                except Exception:  # noqa: BLE001
+                    bits = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+                self.samples.append((time.time(), mhz, bits))
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_flag.set()
+
+    def summary(self, t0, t1):
+        if not self.ok:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'note': 'NVML unavailable'}
+        inside = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples
+        mhz = sorted(s[1] for s in inside)
+        bits = 0
+        for s in inside:
+            bits |= s[2]
+        return {'sm_mhz': mhz[len(mhz) // 2] if mhz else None, 'sm_max_mhz': self.max_mhz,
+                'reasons': [n for b, n in sorted(self.REASONS.items()) if bits & b],
+                'samples': len(inside)}
+
+
+# ------------------------------------------------------------------------------ CPU arm
+def time_oracle(model_name, clips_per_step, steps, warmup, threads=None):
+    """Times oracle/r2p1d_ref.py (the CPU port of the path) on this host.  Returns clips/s."""
+    import torch
+    from oracle import r2p1d_ref as oracle
+    threads = threads or os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    ls = LAYER_SIZES[model_name]
+    model = oracle.build(layer_sizes=ls, seed=0)
+    clips = oracle.synthetic_clips(clips_per_step, seed=1234)
+    for _ in range(warmup):
+        oracle.forward_u8(model, clips)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        oracle.forward_u8(model, clips)
+    dt = time.perf_counter() - t0
+    return clips_per_step * steps / dt, dt / steps, torch.get_num_threads()
+
+
+def run_reference(args, rank):
+    """--impl reference: the CPU implementation of the path on the host cores, rank 0 only."""
+    if rank != 0:
+        return
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    # keep the whole run within a few minutes: probe one step, then cap the step count
+    probe, per_step, threads = time_oracle(args.model, args.ref_clips, 1, 1)
+    budget_s = 150.0
+    steps_run = max(1, min(steps, int(budget_s / max(per_step, 1e-3))))
+    warm_run = min(warmup, 2)
+    value, per_step, threads = time_oracle(args.model, args.ref_clips, steps_run, warm_run)
+    sample = ('%d of %d steps, %d-clip sample of the batch-%d step, oracle/r2p1d_ref.py '
+              '(torch fp32 CPU port; the reference submodule is absent)'
+              % (steps_run, steps, args.ref_clips, args.batch))
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': 'clips/s',
+        'n_gpus': args.gpus, 'steps': steps_run, 'warmup': warm_run,
+        'ms_per_step': per_step * 1e3 * args.batch / args.ref_clips,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic', 'config': base_config(args, args.gpus),
+        'cpu_baseline': {'value': value, 'unit': 'clips/s', 'cores': threads, 'kind': 'port',
+                         'sample': sample},
+        'e2e': {'value': value, 'unit': 'clips/s', 'h2d_bytes_per_step': 0,
+                'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------ GPU arm
+def peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        p = json.load(open(path))
+        return float(p['bf16_tflops']), float(p.get('bf16_tflops_sustained', p['bf16_tflops'])), \
+            'MEASURED_PEAKS.json bf16_tflops (burst, of measured)'
+    except Exception:  # noqa: BLE001
+        return FALLBACK_PEAK_TFLOPS, 1400.0, 'fallback 1.59 PFLOP/s (of fallback)'
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from rnb_b200.engine import R2P1DEngine, random_state_dict
+
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py needs a CUDA device; there is no CPU fallback for the product path')
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    B, K, W = args.batch, max(1, args.steps), max(3, args.warmup)
+    ls = LAYER_SIZES[args.model]
+    sd = random_state_dict(1, 5, 400, ls, seed=0)
+    engine = R2P1DEngine(dev, sd, 1, 5, 400, ls, dtype=args.dtype, max_batch=max(B, 16))
+
+    # inputs larger than L2: a pool of distinct uint8 batches (> 126 MB) visited round-robin
+    pool_n = max(2, -(-160 * 1024 * 1024 // (B * CLIP_BYTES)))
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    pool = torch.randint(0, 256, (pool_n, B, 8, 3, 112, 112), dtype=torch.uint8, device=dev,
+                         generator=g)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+
+    # ---- device-resident throughput ("value")
+    for i in range(W):
+        engine(pool[i % pool_n])
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall0 = time.time()
+    ev0.record()
+    for i in range(K):
+        engine(pool[i % pool_n])
+    ev1.record()
+    barrier()
+    t_wall1 = time.time()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    clocks = sampler.summary(t_wall0, t_wall1)
+
+    # ---- end to end through the public API with HOST buffers: pinned uint8 -> H2D -> forward
+    #      (fused preprocess) -> D2H logits, every step
+    host_in = [torch.randint(0, 256, (B, 8, 3, 112, 112), dtype=torch.uint8).pin_memory()
+               for _ in range(4)]
+    host_out = torch.empty((B, 400), dtype=torch.float32).pin_memory()
+    dev_in = [torch.empty((B, 8, 3, 112, 112), dtype=torch.uint8, device=dev) for _ in range(2)]
+
+    def e2e_step(i):
+        x = dev_in[i & 1]
+        x.copy_(host_in[i % len(host_in)], non_blocking=True)
+        host_out.copy_(engine(x), non_blocking=True)
+
+    for i in range(W):
+        e2e_step(i)
+    barrier()
+    ev0.record()
+    for i in range(K):
+        e2e_step(i)
+    ev1.record()
+    barrier()
+    ms_e2e = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms_e2e], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item())
+
+    # ---- roofline of the dominant kernel (conv_tc_kernel: all convolution launches), measured
+    #      live with CUDA events between launches on the launching stream
+    prof_steps = max(3, min(K, 30))
+    conv_ms, other_ms = 0.0, 0.0
+    per_op = None
+    for i in range(prof_steps):
+        m = engine.profile(pool[i % pool_n])
+        conv_ms += sum(m[1:-1])
+        other_ms += m[0] + m[-1]
+        per_op = m if per_op is None else [a + b for a, b in zip(per_op, m)]
+    conv_ms /= prof_steps
+    other_ms /= prof_steps
+    per_op = [v / prof_steps for v in per_op]
+    sampler.stop()
+    info = engine.op_info()
+    conv_flops = sum(f for _, f, _, _ in info) * B
+    peak_burst, peak_sust, peak_src = peaks()
+    achieved = conv_flops / (conv_ms * 1e-3) / 1e12
+    n_conv = len(info)
+
+    if args.profile_table and rank == 0:
+        with open(args.profile_table, 'w') as f:
+            f.write('| # | convolution | us | GFLOP | TFLOP/s | min GB | GB/s |\n|---|---|---|---|---|---|---|\n')
+            for i, (name, fl, ab, wb) in enumerate(info):
+                us = per_op[i + 1] * 1e3
+                f.write('| %d | %s | %.1f | %.2f | %.0f | %.3f | %.0f |\n' % (
+                    i, name, us, fl * B / 1e9, fl * B / us / 1e6, (ab * B + wb) / 1e9,
+                    (ab * B + wb) / us / 1e3))
+            f.write('| | input staging | %.1f | | | | |\n| | pool + classifier | %.1f | | | | |\n'
+                    % (per_op[0] * 1e3, per_op[-1] * 1e3))
+
+    # ---- CPU baseline beside it (rank 0, N = 1 only): a bounded sample of the same workload
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        probe, per_step, threads = time_oracle(args.model, args.ref_clips, 1, 1)
+        n = max(1, min(8, int(15.0 / max(per_step, 1e-3))))
+        v, per_step, threads = time_oracle(args.model, args.ref_clips, n, 0)
+        cpu = {'value': v, 'unit': 'clips/s', 'cores': threads, 'kind': 'port',
+               'sample': '%d steps of %d clips (of the batch-%d step), oracle/r2p1d_ref.py torch fp32'
+                         % (n, args.ref_clips, B)}
+
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    total_clips = world * K * B
+    line = {
+        'metric': METRIC, 'value': total_clips / (ms * 1e-3), 'unit': 'clips/s',
+        'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': ms / K,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype,
+        'data': 'synthetic',
+        'config': dict(base_config(args, world), **{
+                   'l2': 'inputs larger than L2: %d distinct %.1f MB uint8 batches (%.0f MB) '
+                         'round-robin; per-step activation traffic also exceeds the 126 MB L2'
+                         % (pool_n, B * CLIP_BYTES / 1e6, pool_n * B * CLIP_BYTES / 1e6),
+                   'e2e_path': 'pinned uint8 frames -> H2D -> R2P1DEngine.forward (fused '
+                               'preprocess) -> D2H logits, one stream'}),
+        'e2e': {'value': total_clips / (ms_e2e * 1e-3), 'unit': 'clips/s',
+                'h2d_bytes_per_step': B * CLIP_BYTES, 'd2h_bytes_per_step': B * 400 * 4},
+        'gpu_launches': K * engine.num_launches,
+        'clocks': clocks,
+        'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak_burst,
+                     'unit': 'TFLOP/s', 'frac': achieved / peak_burst, 'traffic': None,
+                     'kernel': 'conv_tc_kernel (%d launches per step)' % n_conv,
+                     'peak_source': peak_src, 'frac_of_sustained': achieved / peak_sust,
+                     'flops_per_launch_avg': conv_flops / n_conv,
+                     'us_per_launch_avg': conv_ms * 1e3 / n_conv,
+                     'kernel_share_of_step': conv_ms / (conv_ms + other_ms),
+                     'whole_step_frac': (GFLOP_PER_CLIP[args.model] * 1e9 * B) /
+                                        (ms / K * 1e-3) / 1e12 / peak_burst},
+        'cpu_baseline': cpu,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under it, as the driver would
+        import subprocess
+        port = 29500 + (os.getpid() % 2000)
+        cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1',
+               '--nproc-per-node', str(args.gpus), '--master-addr', '127.0.0.1',
+               '--master-port', str(port), os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    if args.impl == 'reference':
+        run_reference(args, rank)
+    else:
+        run_b200(args, rank, world, local_rank)
+
+
+if __name__ == '__main__':
+    main()

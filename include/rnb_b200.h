@@ -56,7 +56,8 @@ int rnb_r2p1d_create(const int* layer_sizes, int n_layer_sizes, int start_idx, i
 int rnb_r2p1d_load_param(void* handle, const char* key, const float* host_data, const int64_t* shape,
                          int ndim);
 
-/* Fold BatchNorm (inference statistics) and biases into per-channel scale/shift, repack the
+/* (No counterpart in the reference, where torch modules hold the parameters.)  Fold BatchNorm
+ * (inference statistics) and biases into per-channel scale/shift, repack the
  * weights for the tensor cores, upload everything and allocate the activation arena.  After this
  * call the handle never allocates again except when it first sees a new batch size. */
 int rnb_r2p1d_finalize(void* handle);
@@ -74,10 +75,24 @@ int rnb_r2p1d_forward(void* handle, const void* in, int in_fmt, int batch, void*
  * R2P1DRunner.input_dict at models/r2p1d/model.py:29-33. */
 int rnb_r2p1d_io_shape(void* handle, int which, int64_t shape4[4]);
 
-/* Bookkeeping for benchmarks: algorithmic FLOPs of one forward over `batch` clips (2 x MACs of
- * every convolution and the classifier) and the number of kernels one forward launches. */
+/* Bookkeeping for benchmarks (no counterpart in the reference): algorithmic FLOPs of one forward
+ * over `batch` clips (2 x MACs of every convolution and the classifier) and the number of kernels
+ * one forward launches. */
 double rnb_r2p1d_flops(void* handle, int batch);
 int rnb_r2p1d_num_launches(void* handle);
+
+/* Diagnostics for bench.py and profiles/ (no counterpart in the reference, which times steps with
+ * wall-clock TimeCards only): the same forward pass with a CUDA event recorded on
+ * `stream` between consecutive kernels.  ms[0] = input staging, ms[1 .. n_ops] = the convolutions
+ * in launch order, ms[n_ops + 1] = pool + classifier (or the output layout change); `cap` is the
+ * capacity of ms and must be >= rnb_r2p1d_num_launches().  Synchronises `stream` before returning.
+ * rnb_r2p1d_op_info() describes convolution `op` (0-based): its state_dict prefix, algorithmic
+ * FLOPs per clip, and the bytes per clip it must move at least once (input + output + residual
+ * activations in the handle's dtype; weights are per batch and reported separately). */
+int rnb_r2p1d_profile(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
+                      void* stream, float* ms, int cap);
+int rnb_r2p1d_op_info(void* handle, int op, char* name, int name_cap, double* flops_per_clip,
+                      double* act_bytes_per_clip, double* weight_bytes);
 
 void rnb_r2p1d_destroy(void* handle);
 

@@ -99,6 +99,32 @@ int rnb_r2p1d_forward(void* handle, const void* in, int in_fmt, int batch, void*
   return RNB_OK;
 }
 
+int rnb_r2p1d_profile(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
+                      void* stream, float* ms, int cap) {
+  if (!handle) return fail(RNB_EINVAL, "handle is NULL");
+  std::string err;
+  const int rc = static_cast<rnb::R2P1DModel*>(handle)->profile(
+      in, in_fmt, batch, out, out_fmt, static_cast<cudaStream_t>(stream), ms, cap, &err);
+  if (rc != RNB_OK) {
+    (void)cudaGetLastError();
+    return fail(rc, err);
+  }
+  return RNB_OK;
+}
+
+int rnb_r2p1d_op_info(void* handle, int op, char* name, int name_cap, double* flops_per_clip,
+                      double* act_bytes_per_clip, double* weight_bytes) {
+  auto* m = static_cast<rnb::R2P1DModel*>(handle);
+  if (!m || !m->finalized()) return fail(RNB_ESTATE, "handle not finalized");
+  std::string n;
+  if (!m->op_info(op, &n, flops_per_clip, act_bytes_per_clip, weight_bytes))
+    return fail(RNB_EINVAL, "op index out of range");
+  if (name && name_cap > 0) {
+    snprintf(name, (size_t)name_cap, "%s", n.c_str());
+  }
+  return RNB_OK;
+}
+
 int rnb_r2p1d_io_shape(void* handle, int which, int64_t shape4[4]) {
   if (!handle || !shape4 || (which != 0 && which != 1))
     return fail(RNB_EINVAL, "bad argument to rnb_r2p1d_io_shape");

@@ -327,8 +327,60 @@ double R2P1DModel::flops(int batch) const {
   return f;
 }
 
+bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
+                         double* act_bytes_per_clip, double* weight_bytes) const {
+  if (op < 0 || op >= (int)ops_.size()) return false;
+  const ConvOp& o = ops_[op];
+  const double es = (double)elem_size();
+  double act;
+  if (dtype_ == RNB_DTYPE_BF16) {
+    act = (double)o.g.in_elems(1) + (double)o.g.out_elems(1) * (o.res_slot >= 0 ? 2 : 1);
+  } else {
+    act = (double)o.g.Ti * o.g.Hi * o.g.Wi * o.g.cin +
+          (double)o.g.To * o.g.Ho * o.g.Wo * o.g.cout * (o.res_slot >= 0 ? 2 : 1);
+  }
+  if (name) *name = o.name;
+  if (flops_per_clip) *flops_per_clip = o.g.flops(1);
+  if (act_bytes_per_clip) *act_bytes_per_clip = act * es;
+  if (weight_bytes)
+    *weight_bytes = dtype_ == RNB_DTYPE_BF16
+                        ? (double)o.g.cout_pad() * o.g.k_total() * 2
+                        : (double)o.g.cout * o.g.cin * o.g.kt * o.g.kh * o.g.kw * 4;
+  return true;
+}
+
+int R2P1DModel::profile(const void* in, int in_fmt, int batch, void* out, int out_fmt,
+                        cudaStream_t stream, float* ms, int cap, std::string* err) {
+  const int n = num_launches();
+  if (!ms || cap < n) {
+    if (err) *err = "profile: ms buffer too small";
+    return RNB_EINVAL;
+  }
+  std::vector<cudaEvent_t> ev(n + 1, nullptr);
+  for (auto& e : ev)
+    if (!cuda_ok(cudaEventCreate(&e), "cudaEventCreate", err)) return RNB_ECUDA;
+  int rc = forward(in, in_fmt, batch, out, out_fmt, stream, err, ev.data());
+  if (rc == RNB_OK && !cuda_ok(cudaStreamSynchronize(stream), "profile sync", err)) rc = RNB_ECUDA;
+  if (rc == RNB_OK) {
+    for (int i = 0; i < n; ++i) {
+      ms[i] = 0.f;
+      if (batch > 0 && !cuda_ok(cudaEventElapsedTime(&ms[i], ev[i], ev[i + 1]), "elapsed", err)) {
+        rc = RNB_ECUDA;
+        break;
+      }
+    }
+  }
+  for (auto& e : ev)
+    if (e) cudaEventDestroy(e);
+  return rc;
+}
+
 int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int out_fmt,
-                        cudaStream_t stream, std::string* err) {
+                        cudaStream_t stream, std::string* err, cudaEvent_t* events) {
+  int ev_idx = 0;
+  auto mark = [&]() {
+    if (events) cudaEventRecord(events[ev_idx++], stream);
+  };
   if (!finalized_) {
     if (err) *err = "forward before finalize";
     return RNB_ESTATE;
@@ -352,6 +404,7 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
     return RNB_EINVAL;
   }
   cudaError_t e = cudaSuccess;
+  mark();
 
   // ---- stage the input into the arena
   const int S_in = in_dims_.T * in_dims_.H * in_dims_.W;
@@ -386,6 +439,7 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
     }
   }
   if (!cuda_ok(e, "input staging", err)) return RNB_ECUDA;
+  mark();
 
   // ---- convolutions
   if (tc) {
@@ -410,6 +464,7 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
     for (size_t i = 0; i < ops_.size(); ++i) {
       if (!cuda_ok(launch_conv_tc(it->second[i], num_sms_, stream), ops_[i].name.c_str(), err))
         return RNB_ECUDA;
+      mark();
     }
   } else {
     for (const ConvOp& op : ops_) {
@@ -427,6 +482,7 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
       rp.pt = op.g.pt; rp.ph = op.g.ph; rp.pw = op.g.pw;
       rp.relu = op.relu ? 1 : 0;
       if (!cuda_ok(launch_conv_ref(rp, stream), op.name.c_str(), err)) return RNB_ECUDA;
+      mark();
     }
   }
 
@@ -448,6 +504,7 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
                         cudaMemcpyDeviceToDevice, stream);
   }
   if (!cuda_ok(e, "output stage", err)) return RNB_ECUDA;
+  mark();
   return RNB_OK;
 }
 

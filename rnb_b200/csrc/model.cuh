@@ -40,8 +40,13 @@ class R2P1DModel {
   bool load_param(const char* key, const float* data, const int64_t* shape, int ndim,
                   std::string* err);
   int finalize(std::string* err);  // RNB_* code
+  // `events`, when given, receives num_launches()+1 events recorded around every kernel
   int forward(const void* in, int in_fmt, int batch, void* out, int out_fmt, cudaStream_t stream,
-              std::string* err);
+              std::string* err, cudaEvent_t* events = nullptr);
+  int profile(const void* in, int in_fmt, int batch, void* out, int out_fmt, cudaStream_t stream,
+              float* ms, int cap, std::string* err);
+  bool op_info(int op, std::string* name, double* flops_per_clip, double* act_bytes_per_clip,
+               double* weight_bytes) const;
   void io_shape(int which, int64_t shape4[4]) const;
   double flops(int batch) const;
   int num_launches() const { return (int)ops_.size() + 2; }

@@ -175,13 +175,32 @@ class R2P1DEngine:
     def num_launches(self):
         return int(self.lib.rnb_r2p1d_num_launches(self._handle))
 
+    def op_info(self):
+        """[(state_dict prefix, FLOPs per clip, activation bytes per clip, weight bytes)] per conv."""
+        info = []
+        for i in range(self.num_launches - 2):
+            name = ctypes.create_string_buffer(256)
+            f, a, w = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+            _lib.check(self.lib.rnb_r2p1d_op_info(self._handle, i, name, 256, ctypes.byref(f),
+                                                  ctypes.byref(a), ctypes.byref(w)))
+            info.append((name.value.decode(), f.value, a.value, w.value))
+        return info
+
+    def profile(self, x):
+        """Per-kernel milliseconds of one forward (CUDA events between launches); synchronises."""
+        x, fmt, batch = self._check_input(x)
+        out = self._out[:batch]
+        out_fmt = _lib.FMT_F32_LOGITS if self.end_index == 5 else _lib.FMT_F32_NCDHW
+        n = self.num_launches
+        ms = (ctypes.c_float * n)()
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self.lib.rnb_r2p1d_profile(self._handle, ctypes.c_void_p(x.data_ptr()), fmt,
+                                              batch, ctypes.c_void_p(out.data_ptr()), out_fmt,
+                                              ctypes.c_void_p(stream), ms, n))
+        return list(ms)
+
     # ------------------------------------------------------------------ forward
-    def forward(self, x, out=None):
-        """``x``: uint8 (B, 8, 3, 112, 112) loader frames (start layer 1 only) or fp32
-        (B, C, T, H, W).  Returns fp32 (B, num_classes) logits, or fp32 (B, C, T, H, W) activations
-        when the range ends before layer 5.  The result aliases an engine-owned buffer that the
-        next call overwrites, unless ``out`` is given.  Asynchronous on the current stream.
-        """
+    def _check_input(self, x):
         batch = int(x.shape[0])
         if x.device != self.device and not (x.is_cuda and x.device.index == self.device_index):
             raise ValueError('input lives on %s, engine on %s' % (x.device, self.device))
@@ -197,9 +216,18 @@ class R2P1DEngine:
             raise TypeError('input must be uint8 frames or float32 activations, got %s' % x.dtype)
         if not x.is_contiguous():
             x = x.contiguous()
+        if batch > self.max_batch:
+            raise ValueError('batch %d exceeds max_batch %d' % (batch, self.max_batch))
+        return x, fmt, batch
+
+    def forward(self, x, out=None):
+        """``x``: uint8 (B, 8, 3, 112, 112) loader frames (start layer 1 only) or fp32
+        (B, C, T, H, W).  Returns fp32 (B, num_classes) logits, or fp32 (B, C, T, H, W) activations
+        when the range ends before layer 5.  The result aliases an engine-owned buffer that the
+        next call overwrites, unless ``out`` is given.  Asynchronous on the current stream.
+        """
+        x, fmt, batch = self._check_input(x)
         if out is None:
-            if batch > self.max_batch:
-                raise ValueError('batch %d exceeds max_batch %d' % (batch, self.max_batch))
             out = self._out[:batch]
         out_fmt = _lib.FMT_F32_LOGITS if self.end_index == 5 else _lib.FMT_F32_NCDHW
         stream = torch.cuda.current_stream(self.device).cuda_stream
