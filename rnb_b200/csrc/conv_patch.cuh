@@ -1,0 +1,53 @@
+// "Patch" variant of the tcgen05 convolution for stride-1 layers whose weights fit in shared memory.
+//
+// conv_tc_kernel re-reads the 128-row activation tile once per filter tap and streams the weights
+// through shared memory for every tile, so its L2->SM traffic is ~taps x (A + B) per tile (983 MB
+// per conv2 launch, profiles/r01_ncu_conv_tc_v1.md).  Here the CTA loads ALL packed weights once,
+// and per tile ONE activation patch (tile + halo); every filter tap is the same patch read at a row
+// offset, expressed only in the UMMA shared-memory descriptor.  (Measured on B200: the 128-byte
+// swizzle is a function of the shared-memory ADDRESS bits, so a descriptor whose start address is
+// shifted by whole 128-byte rows reads correctly with the base-offset field left at zero; filling
+// that field with address bits 7-9 gives wrong results.  profiles/r01_test_conv_patch.log)
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "conv_tc.cuh"
+
+namespace rnb {
+
+constexpr int kPatchMaxKb = 4;  // 64-channel blocks per patch
+
+struct ConvPatchParams {
+  alignas(64) CUtensorMap a_map;  // activation (C, W, H, T, B), box (64, pbox_w, pbox_h, pbox_t, 1)
+  alignas(64) CUtensorMap b_map;  // packed weights (K_total, N), box (64, N)
+  const float* shift;
+  const __nv_bfloat16* residual;
+  __nv_bfloat16* y;     // output (B, To, Ho, Wo, cout_pad): written with plain 32-byte stores
+  int nkb;              // 64-channel blocks of the input (cin_pad / 64 rounded up)
+  int cin_pad;
+  int patch_rows;       // rows (positions) of one patch block = pbox_w * pbox_h * pbox_t
+  int num_taps;
+  int n;                // output channels = accumulator columns (multiple of 16, <= 256)
+  // output tile: tw x th x tt positions, laid out in the accumulator with power-of-two pitches
+  int tw, th, tt;
+  int lpw, lph;         // log2 of the row pitches: row = (t << (lpw + lph)) + (h << lpw) + w
+  int tiles_w, tiles_h, tiles_t, tiles_b;
+  int aw, ah, at;       // patch origin relative to the tile origin (-1 where the filter extends)
+  int Wo, Ho, To, B;
+  int cout_pad;
+  int relu;
+  long long* dbg;       // optional: 8 cycle counters per CTA (see conv_patch.cu), or nullptr
+  int16_t tap_shift[kMaxTaps];  // row offset of each tap inside the patch
+};
+
+inline int conv_patch_smem_bytes(int nkb, int patch_rows, int num_taps, int n) {
+  return 1024 + num_taps * nkb * n * 128 + 2 * nkb * patch_rows * 128 + 1024 /*slack rows*/ + 256 +
+         kMaxBlockN * 4;
+}
+
+cudaError_t launch_conv_patch(const ConvPatchParams& p, int num_sms, cudaStream_t stream);
+
+}  // namespace rnb

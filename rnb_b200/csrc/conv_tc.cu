@@ -44,18 +44,16 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvTcParams& p, int tile
   return c;
 }
 
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<uint32_t*>(&v);
-}
 
 }  // namespace
 
+template <bool kRes, bool kRelu>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  const int warp = threadIdx.x >> 5;
+  // shuffle-broadcast so the compiler knows these are warp-uniform (role branches, TMEM address)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
   const uint32_t a_bytes = kTileM * p.bk * 2;
@@ -69,6 +67,7 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   const uint32_t tmem_full_bar = bars + 16 * p.num_stages;
   const uint32_t tmem_empty_bar = tmem_full_bar + 16;
   const uint32_t tmem_ptr_smem = tmem_empty_bar + 16;
+  const uint32_t shift_tab = bars + 256;  // kMaxBlockN floats
 
   const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b * p.n_tiles;
 
@@ -82,7 +81,7 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(tmem_full_bar + 8 * s, 1);
-      ptx::mbar_init(tmem_empty_bar + 8 * s, 128);
+      ptx::mbar_init(tmem_empty_bar + 8 * s, kEpiThreads);
     }
     ptx::fence_mbar_init();
   }
@@ -95,151 +94,165 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   ptx::tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
+  tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
 
   if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      uint32_t stage = 0, phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const TileCoord tc = decode_tile(p, tile);
-        for (int tap = 0; tap < p.num_taps; ++tap) {
-          const void* amap = &p.a_map[p.tap_map[tap]];
-          const int cw = tc.w0 + p.tap_dw[tap];
-          const int ch = tc.h0 + p.tap_dh[tap];
-          const int ct = tc.t0 + p.tap_dt[tap];
-          const int coff = p.tap_coff[tap];
-          const int koff = p.tap_koff[tap];
-          for (int kb = 0; kb < p.kb_per_tap; ++kb) {
-            ptx::mbar_wait(empty_bar + 8 * stage, phase ^ 1);
-            const uint32_t fb = full_bar + 8 * stage;
-            const uint32_t sa = smem_base + stage * stage_bytes;
-            ptx::mbar_expect_tx(fb, stage_bytes);
-            ptx::tma_load_5d(sa, amap, fb, coff + kb * p.bk, cw, ch, ct, tc.b0);
-            ptx::tma_load_2d(sa + a_bytes, &p.b_map, fb, koff + kb * p.bk, tc.n0);
-            if (++stage == (uint32_t)p.num_stages) {
-              stage = 0;
-              phase ^= 1;
-            }
+    // ------------------------------------------------------------------ TMA producer (warp-wide,
+    // one elected lane issues; see conv_patch.cu for why the roles are not run under lane == 0)
+    uint32_t stage = 0, phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const TileCoord tc = decode_tile(p, tile);
+      for (int tap = 0; tap < p.num_taps; ++tap) {
+        const void* amap = &p.a_map[p.tap_map[tap]];
+        const int cw = tc.w0 + p.tap_dw[tap];
+        const int ch = tc.h0 + p.tap_dh[tap];
+        const int ct = tc.t0 + p.tap_dt[tap];
+        const int coff = p.tap_coff[tap];
+        const int koff = p.tap_koff[tap];
+        for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+          ptx::mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+          const uint32_t fb = full_bar + 8 * stage;
+          const uint32_t sa = smem_base + stage * stage_bytes;
+          ptx::mbar_expect_tx_elect(fb, stage_bytes);
+          ptx::tma_load_5d_elect(sa, amap, fb, coff + kb * p.bk, cw, ch, ct, tc.b0);
+          ptx::tma_load_2d_elect(sa + a_bytes, &p.b_map, fb, koff + kb * p.bk, tc.n0);
+          if (++stage == (uint32_t)p.num_stages) {
+            stage = 0;
+            phase ^= 1;
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      const uint32_t swz = p.bk * 2;  // bytes per operand row == swizzle span
-      uint32_t stage = 0, phase = 0;
-      int local = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
-        const TileCoord tc = decode_tile(p, tile);
-        const uint32_t acc = local & 1;
-        const uint32_t acc_phase = (local >> 1) & 1;
-        const uint32_t idesc = ptx::make_idesc_bf16_m128((uint32_t)tc.ncols);
-        const uint32_t tmem_d = tmem_base + acc * kMaxBlockN;
-        ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1);
-        ptx::tc_fence_after();
-        uint32_t accumulate = 0;
-        for (int tap = 0; tap < p.num_taps; ++tap) {
-          for (int kb = 0; kb < p.kb_per_tap; ++kb) {
-            ptx::mbar_wait(full_bar + 8 * stage, phase);
-            ptx::tc_fence_after();
-            const uint32_t sa = smem_base + stage * stage_bytes;
-            const uint64_t adesc = ptx::make_kmajor_desc(sa, swz);
-            const uint64_t bdesc = ptx::make_kmajor_desc(sa + a_bytes, swz);
-            const int ksteps = min(p.bk, p.cin_pad - kb * p.bk) >> 4;
-            for (int k = 0; k < ksteps; ++k) {
-              // advancing 16 bf16 = 32 bytes along K inside the swizzle span: +2 in the address field
-              ptx::umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, accumulate);
-              accumulate = 1;
-            }
-            ptx::umma_commit(empty_bar + 8 * stage);
-            if (++stage == (uint32_t)p.num_stages) {
-              stage = 0;
-              phase ^= 1;
-            }
+    // ------------------------------------------------------------------ MMA issuer (warp-wide)
+    const uint32_t swz = p.bk * 2;  // bytes per operand row == swizzle span
+    uint32_t stage = 0, phase = 0;
+    int local = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      const TileCoord tc = decode_tile(p, tile);
+      const uint32_t acc = local & 1;
+      const uint32_t acc_phase = (local >> 1) & 1;
+      const uint32_t idesc = ptx::make_idesc_bf16_m128((uint32_t)tc.ncols);
+      const uint32_t tmem_d = tmem_base + acc * kMaxBlockN;
+      ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1);
+      ptx::tc_fence_after();
+      uint32_t accumulate = 0;
+      for (int tap = 0; tap < p.num_taps; ++tap) {
+        for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+          ptx::mbar_wait(full_bar + 8 * stage, phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = smem_base + stage * stage_bytes;
+          const uint64_t adesc = ptx::make_kmajor_desc(sa, swz);
+          const uint64_t bdesc = ptx::make_kmajor_desc(sa + a_bytes, swz);
+          const int ksteps = min(p.bk, p.cin_pad - kb * p.bk) >> 4;
+          // advancing 16 bf16 = 32 bytes along K inside the swizzle span: +2 in the address field
+          ptx::umma_bf16_elect(tmem_d, adesc, bdesc, idesc, accumulate);
+          if (ksteps > 1) ptx::umma_bf16_elect(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
+          if (ksteps > 2) ptx::umma_bf16_elect(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
+          if (ksteps > 3) ptx::umma_bf16_elect(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
+          accumulate = 1;
+          ptx::umma_commit_elect(empty_bar + 8 * stage);
+          if (++stage == (uint32_t)p.num_stages) {
+            stage = 0;
+            phase ^= 1;
           }
         }
-        ptx::umma_commit(tmem_full_bar + 8 * acc);
       }
+      ptx::umma_commit_elect(tmem_full_bar + 8 * acc);
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (128 threads)
+    // ------------------------------------------------------------------ epilogue (256 threads)
+    // Two warps share each TMEM lane quarter and take alternate 16-column chunks.
+    const int ew = warp - 2;          // 0..7
     const int q = warp & 3;           // TMEM lane quarter this warp may read
+    const int half = ew >> 2;         // which chunks of a sub-tile this warp converts
     const int row = q * 32 + lane;    // output position inside the tile
-    const bool store_thread = (threadIdx.x == 64);
+    const int et = threadIdx.x - 64;  // 0..255
+    const bool store_thread = (et == 0);
     const int lbb_shift = p.lbw + p.lbh + p.lbt;
     const int iw = row & ((1 << p.lbw) - 1);
     const int ih = (row >> p.lbw) & ((1 << p.lbh) - 1);
     const int it = (row >> (p.lbw + p.lbh)) & ((1 << p.lbt) - 1);
     const int ib = row >> lbb_shift;
+    const uint32_t rowaddr_off = row * 128;
+    const uint32_t rsw = row & 7;
     int local = 0;
     uint32_t nstore = 0;
+    int table_n0 = -1;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
       const TileCoord tc = decode_tile(p, tile);
       const uint32_t acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
-      const int w = tc.w0 + iw, h = tc.h0 + ih, t = tc.t0 + it, b = tc.b0 + ib;
-      const bool row_valid = (w < p.Wo) && (h < p.Ho) && (t < p.To) && (b < p.B);
       const __nv_bfloat16* res_row = nullptr;
-      if (p.residual != nullptr && row_valid) {
-        res_row = p.residual + ((((size_t)b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad;
+      if (kRes) {
+        const int w = tc.w0 + iw, h = tc.h0 + ih, t = tc.t0 + it, b = tc.b0 + ib;
+        if ((w < p.Wo) && (h < p.Ho) && (t < p.To) && (b < p.B))
+          res_row = p.residual + ((((size_t)b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad;
+      }
+      if (tc.n0 != table_n0) {
+        // per-channel shift of this channel tile -> shared memory (visible after the first barrier
+        // below; the previous tile's readers are all past their last barrier)
+        if (et < tc.ncols) {
+          const float v = __ldg(p.shift + tc.n0 + et);
+          asm volatile("st.shared.f32 [%0], %1;\n" ::"r"(shift_tab + et * 4), "f"(v) : "memory");
+        }
+        table_n0 = tc.n0;
       }
       ptx::mbar_wait(tmem_full_bar + 8 * acc, acc_phase);
       ptx::tc_fence_after();
       const uint32_t taddr_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kMaxBlockN;
       const int nsub = (tc.ncols + 63) >> 6;
       for (int sub = 0; sub < nsub; ++sub) {
-        const int cols = min(64, tc.ncols - sub * 64);  // multiple of 16
-        const int nchunk = cols >> 4;
+        const int nchunk = min(64, tc.ncols - sub * 64) >> 4;  // 16-column chunks in this sub-tile
         const uint32_t buf = staging + (nstore & 1) * kStagingBytes;
         // the staging buffer used two stores ago must have been read by its TMA store
         if (store_thread) ptx::tma_store_wait_read<1>();
-        ptx::named_bar_sync(1, 128);
-#pragma unroll 1
-        for (int cchunk = 0; cchunk < nchunk; ++cchunk) {
+        ptx::named_bar_sync(1, kEpiThreads);
+        for (int cchunk = half; cchunk < nchunk; cchunk += 2) {
           uint32_t v[16];
-          ptx::tmem_ld16(taddr_row + sub * 64 + cchunk * 16, v);
-          const int n = tc.n0 + sub * 64 + cchunk * 16;
-          float sc[16], sh[16];
+          const int col = sub * 64 + cchunk * 16;
+          ptx::tmem_ld16(taddr_row + col, v);
+          uint64_t sh2[8];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.scale + n) + j);
-            const float4 h4 = __ldg(reinterpret_cast<const float4*>(p.shift + n) + j);
-            sc[4 * j] = s4.x; sc[4 * j + 1] = s4.y; sc[4 * j + 2] = s4.z; sc[4 * j + 3] = s4.w;
-            sh[4 * j] = h4.x; sh[4 * j + 1] = h4.y; sh[4 * j + 2] = h4.z; sh[4 * j + 3] = h4.w;
+            asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];\n"
+                         : "=l"(sh2[2 * j]), "=l"(sh2[2 * j + 1])
+                         : "r"(shift_tab + (col + 4 * j) * 4));
           }
-          float r[16];
+          uint64_t r2[8];
+          if (kRes) {
+            uint32_t rw[8];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) r[j] = 0.f;
-          if (res_row != nullptr) {
-            const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(res_row + n));
-            const uint4 r1 = __ldg(reinterpret_cast<const uint4*>(res_row + n) + 1);
-            const uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              r[2 * j] = __uint_as_float(rw[j] << 16);
-              r[2 * j + 1] = __uint_as_float(rw[j] & 0xffff0000u);
+            for (int j = 0; j < 8; ++j) rw[j] = 0u;
+            if (res_row != nullptr) {
+              const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(res_row + tc.n0 + col));
+              const uint4 r1 = __ldg(reinterpret_cast<const uint4*>(res_row + tc.n0 + col) + 1);
+              rw[0] = r0.x; rw[1] = r0.y; rw[2] = r0.z; rw[3] = r0.w;
+              rw[4] = r1.x; rw[5] = r1.y; rw[6] = r1.z; rw[7] = r1.w;
             }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              r2[j] = ptx::pack_f32x2(__uint_as_float(rw[j] << 16),
+                                      __uint_as_float(rw[j] & 0xffff0000u));
           }
           ptx::tmem_ld_wait();
-          float o[16];
+          uint32_t o[8];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            float x = fmaf(__uint_as_float(v[j]), sc[j], sh[j]) + r[j];
-            o[j] = p.relu ? fmaxf(x, 0.f) : x;
+          for (int j = 0; j < 8; ++j) {
+            uint64_t x = ptx::add_f32x2(
+                ptx::pack_f32x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), sh2[j]);
+            if (kRes) x = ptx::add_f32x2(x, r2[j]);
+            o[j] = ptx::cvt_bf16x2<kRelu>(x);
           }
           // two 16-byte chunks of this row; 128-byte swizzle: chunk index XOR (row mod 8)
-          const int c0 = cchunk * 2;
-          const uint32_t rowaddr = buf + row * 128;
-          const uint32_t a0 = rowaddr + (((c0) ^ (row & 7)) << 4);
-          const uint32_t a1 = rowaddr + (((c0 + 1) ^ (row & 7)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(a0),
-                       "r"(pack_bf16x2(o[0], o[1])), "r"(pack_bf16x2(o[2], o[3])),
-                       "r"(pack_bf16x2(o[4], o[5])), "r"(pack_bf16x2(o[6], o[7]))
+          const uint32_t rowaddr = buf + rowaddr_off;
+          const uint32_t a0 = rowaddr + (((cchunk * 2) ^ rsw) << 4);
+          const uint32_t a1 = rowaddr + (((cchunk * 2 + 1) ^ rsw) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(a0), "r"(o[0]), "r"(o[1]),
+                       "r"(o[2]), "r"(o[3])
                        : "memory");
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(a1),
-                       "r"(pack_bf16x2(o[8], o[9])), "r"(pack_bf16x2(o[10], o[11])),
-                       "r"(pack_bf16x2(o[12], o[13])), "r"(pack_bf16x2(o[14], o[15]))
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(a1), "r"(o[4]), "r"(o[5]),
+                       "r"(o[6]), "r"(o[7])
                        : "memory");
         }
         if (sub == nsub - 1) {
@@ -248,7 +261,7 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
           ptx::mbar_arrive(tmem_empty_bar + 8 * acc);
         }
         ptx::fence_proxy_async_smem();
-        ptx::named_bar_sync(1, 128);
+        ptx::named_bar_sync(1, kEpiThreads);
         if (store_thread) {
           ptx::tma_store_5d(&p.d_map, buf, tc.n0 + sub * 64, tc.w0, tc.h0, tc.t0, tc.b0);
           ptx::tma_store_commit();
@@ -267,19 +280,33 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   }
 }
 
+namespace {
+template <bool kRes, bool kRelu>
+cudaError_t launch_variant(const ConvTcParams& p, int grid, int smem, cudaStream_t stream) {
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
+    e = cudaFuncSetAttribute(conv_tc_kernel<kRes, kRelu>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (e != cudaSuccess) return e;
+    configured[dev] = true;
+  }
+  conv_tc_kernel<kRes, kRelu><<<grid, kConvThreads, smem, stream>>>(p);
+  return cudaGetLastError();
+}
+}  // namespace
+
 cudaError_t launch_conv_tc(const ConvTcParams& p, int num_sms, cudaStream_t stream) {
   const int smem = conv_tc_smem_bytes(p.bk, p.block_n, p.num_stages);
-  static int configured_smem = 0;
-  if (smem > configured_smem) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemLimit);
-    if (e != cudaSuccess) return e;
-    configured_smem = kSmemLimit;
-  }
   const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b * p.n_tiles;
   const int grid = total_tiles < num_sms ? total_tiles : num_sms;
-  conv_tc_kernel<<<grid, kConvThreads, smem, stream>>>(p);
-  return cudaGetLastError();
+  const bool res = p.residual != nullptr, relu = p.relu != 0;
+  if (res) return relu ? launch_variant<true, true>(p, grid, smem, stream)
+                       : launch_variant<true, false>(p, grid, smem, stream);
+  return relu ? launch_variant<false, true>(p, grid, smem, stream)
+              : launch_variant<false, false>(p, grid, smem, stream);
 }
 
 }  // namespace rnb

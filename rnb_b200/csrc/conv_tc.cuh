@@ -11,7 +11,8 @@ constexpr int kMaxTaps = 32;
 constexpr int kTileM = 128;          // output positions per tile = TMEM lanes
 constexpr int kMaxBlockN = 256;      // accumulator columns per tile
 constexpr int kTmemCols = 512;       // two accumulator buffers
-constexpr int kConvThreads = 192;    // warp0 TMA, warp1 MMA, warps2-5 epilogue
+constexpr int kConvThreads = 320;    // warp0 TMA, warp1 MMA, warps2-9 epilogue
+constexpr int kEpiThreads = 256;
 constexpr int kStagingBytes = 16384; // one 128 x 64 bf16 output sub-tile
 constexpr int kSmemLimit = 232448;   // 227 KB
 
@@ -22,8 +23,7 @@ struct ConvTcParams {
   alignas(64) CUtensorMap a_map[4];  // activation views, dims (C, W, H, T, B), bf16
   alignas(64) CUtensorMap b_map;     // packed weights, dims (K_total, N_rows), bf16, K-major
   alignas(64) CUtensorMap d_map;     // output, dims (C, W, H, T, B), bf16
-  const float* scale;                // per output channel, length n_tiles*block_n
-  const float* shift;
+  const float* shift;                // per output channel (BatchNorm scale is folded into the weights)
   const __nv_bfloat16* residual;     // same layout as the output, or nullptr
   int num_taps;
   int cin_pad;      // input channels per tap (multiple of 16)
@@ -49,7 +49,7 @@ inline int conv_tc_stage_bytes(int bk, int block_n) { return (kTileM + block_n) 
 // Dynamic shared memory the kernel needs for a given configuration.
 inline int conv_tc_smem_bytes(int bk, int block_n, int stages) {
   return 1024 /*alignment slack*/ + stages * conv_tc_stage_bytes(bk, block_n) + 2 * kStagingBytes +
-         256 /*barriers*/;
+         256 /*barriers*/ + kMaxBlockN * 4 /*shift table*/;
 }
 
 cudaError_t launch_conv_tc(const ConvTcParams& p, int num_sms, cudaStream_t stream);

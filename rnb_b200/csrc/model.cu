@@ -268,7 +268,7 @@ int R2P1DModel::finalize(std::string* err) {
               cuda_ok(cudaMemcpy(op.d_shift, sh.data(), np * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err);
     if (ok && dtype_ == RNB_DTYPE_BF16) {
       std::vector<uint16_t> packed;
-      pack_conv_weights_tc(op.g, op.w.data(), &packed);
+      pack_conv_weights_tc(op.g, op.w.data(), op.scale.data(), &packed);
       ok = cuda_ok(cudaMalloc(&op.d_w, packed.size() * 2), "cudaMalloc(weights)", err) &&
            cuda_ok(cudaMemcpy(op.d_w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice),
                    "cudaMemcpy(weights)", err);
@@ -445,16 +445,23 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
   if (tc) {
     auto it = plans_.find(batch);
     if (it == plans_.end()) {
-      std::vector<ConvTcParams> plan(ops_.size());
+      std::vector<OpPlan> plan(ops_.size());
       for (size_t i = 0; i < ops_.size(); ++i) {
         const ConvOp& op = ops_[i];
         std::string perr;
-        if (!build_conv_tc_params(
-                op.g, batch, (const __nv_bfloat16*)slots_[op.in_slot],
-                (const __nv_bfloat16*)op.d_w, (__nv_bfloat16*)slots_[op.out_slot], op.d_scale,
-                op.d_shift,
-                op.res_slot >= 0 ? (const __nv_bfloat16*)slots_[op.res_slot] : nullptr, op.relu,
-                num_sms_, &plan[i], &perr)) {
+        const __nv_bfloat16* x = (const __nv_bfloat16*)slots_[op.in_slot];
+        const __nv_bfloat16* w = (const __nv_bfloat16*)op.d_w;
+        __nv_bfloat16* y = (__nv_bfloat16*)slots_[op.out_slot];
+        const __nv_bfloat16* res =
+            op.res_slot >= 0 ? (const __nv_bfloat16*)slots_[op.res_slot] : nullptr;
+        plan[i].patch = conv_patch_applicable(op.g);
+        const bool ok =
+            plan[i].patch
+                ? build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
+                                          &plan[i].pp, &perr)
+                : build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_,
+                                       &plan[i].tc, &perr);
+        if (!ok) {
           if (err) *err = op.name + ": " + perr;
           return RNB_ECUDA;
         }
@@ -462,8 +469,10 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
       it = plans_.emplace(batch, std::move(plan)).first;
     }
     for (size_t i = 0; i < ops_.size(); ++i) {
-      if (!cuda_ok(launch_conv_tc(it->second[i], num_sms_, stream), ops_[i].name.c_str(), err))
-        return RNB_ECUDA;
+      const OpPlan& op = it->second[i];
+      const cudaError_t le = op.patch ? launch_conv_patch(op.pp, num_sms_, stream)
+                                      : launch_conv_tc(op.tc, num_sms_, stream);
+      if (!cuda_ok(le, ops_[i].name.c_str(), err)) return RNB_ECUDA;
       mark();
     }
   } else {

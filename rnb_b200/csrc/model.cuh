@@ -80,7 +80,14 @@ class R2P1DModel {
   size_t slot_elems_per_clip_[NUM_SLOTS] = {};
   float* d_fc_w_ = nullptr;
   float* d_fc_b_ = nullptr;
-  std::map<int, std::vector<ConvTcParams>> plans_;  // tensor-core launch plans per batch size
+  // tensor-core launch plan of one convolution for one batch size: the patch kernel where it
+  // applies (stride-1 3x3 / 3x1x1 layers whose weights fit in shared memory), else the tap kernel
+  struct OpPlan {
+    bool patch = false;
+    ConvTcParams tc;
+    ConvPatchParams pp;
+  };
+  std::map<int, std::vector<OpPlan>> plans_;
 };
 
 }  // namespace rnb

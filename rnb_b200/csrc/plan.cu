@@ -22,12 +22,14 @@ float bf16_bits_to_f32(uint16_t b) {
   return f;
 }
 
-void pack_conv_weights_tc(const ConvGeom& g, const float* w, std::vector<uint16_t>* packed) {
+void pack_conv_weights_tc(const ConvGeom& g, const float* w, const float* scale,
+                          std::vector<uint16_t>* packed) {
   const int kp = g.k_total();
   const int cp = g.cin_pad();
   packed->assign((size_t)g.cout_pad() * kp, 0);
   for (int n = 0; n < g.cout; ++n) {
     uint16_t* row = packed->data() + (size_t)n * kp;
+    const float sc = scale ? scale[n] : 1.f;
     for (int c = 0; c < g.cin; ++c)
       for (int dt = 0; dt < g.kt; ++dt)
         for (int dh = 0; dh < g.kh; ++dh)
@@ -39,7 +41,7 @@ void pack_conv_weights_tc(const ConvGeom& g, const float* w, std::vector<uint16_
             } else {
               k = (size_t)((dt * g.kh + dh) * g.kw + dw) * cp + c;
             }
-            row[k] = f32_to_bf16_bits(v);
+            row[k] = f32_to_bf16_bits(v * sc);
           }
   }
 }
@@ -150,8 +152,7 @@ struct View {
 }  // namespace
 
 bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
-                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* scale,
-                          const float* shift, const __nv_bfloat16* residual, bool relu, int num_sms,
+                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift, const __nv_bfloat16* residual, bool relu, int num_sms,
                           ConvTcParams* out, std::string* err) {
   ConvTcParams& p = *out;
   memset(&p, 0, sizeof p);
@@ -166,7 +167,6 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
     if (err) *err = "conv_tc: a strided dimension must have even extent";
     return false;
   }
-  p.scale = scale;
   p.shift = shift;
   p.residual = residual;
   p.relu = relu ? 1 : 0;
@@ -203,7 +203,7 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
     p.n_tiles = ceil_div(np, p.block_n);
   }
   const int stage_bytes = conv_tc_stage_bytes(p.bk, p.block_n);
-  int stages = (kSmemLimit - 1024 - 2 * kStagingBytes - 256) / stage_bytes;
+  int stages = (kSmemLimit - conv_tc_smem_bytes(p.bk, p.block_n, 0)) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) {
     if (err) *err = "conv_tc: pipeline does not fit in shared memory";
@@ -288,6 +288,99 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                                  (uint64_t)g.To * g.Ho * g.Wo * np * 2};
     const uint32_t box[5] = {64u, (uint32_t)bw, (uint32_t)bh, (uint32_t)bt, (uint32_t)bb};
     if (!encode_bf16(&p.d_map, y, 5, dims, strides, box, 128, err)) return false;
+  }
+  return true;
+}
+
+namespace {
+struct PatchShape {
+  bool ok = false;
+  bool spatial = false;
+  int nkb = 0, patch_rows = 0, taps = 0;
+  int tw = 0, th = 0, tt = 0, lpw = 0, lph = 0;
+  int pbw = 0, pbh = 0, pbt = 0;  // patch box extent
+};
+
+PatchShape patch_shape(const ConvGeom& g) {
+  PatchShape s;
+  if (g.stem_unfolded || g.st != 1 || g.sh != 1 || g.sw != 1) return s;
+  if (g.cout_pad() > kMaxBlockN) return s;
+  s.nkb = ceil_div(g.cin_pad(), 64);
+  if (s.nkb > kPatchMaxKb) return s;
+  if (g.kt == 1 && g.kh == 3 && g.kw == 3 && g.ph == 1 && g.pw == 1 && g.pt == 0) {
+    // one frame, 8 rows of 14 columns; accumulator rows use a pitch of 16 so that a filter tap is
+    // a pure row offset (dh * 16 + dw) inside the 10 x 16 patch
+    s.spatial = true;
+    s.taps = 9;
+    s.tw = 14; s.th = 8; s.tt = 1; s.lpw = 4; s.lph = 3;
+    s.pbw = 16; s.pbh = 10; s.pbt = 1;
+  } else if (g.kt == 3 && g.kh == 1 && g.kw == 1 && g.pt == 1 && g.ph == 0 && g.pw == 0) {
+    // 16 positions (8 x 2) by up to 8 frames; a tap is an offset of 16 rows in the 10-frame patch
+    s.taps = 3;
+    s.tw = 8; s.th = 2; s.tt = g.To < 8 ? g.To : 8; s.lpw = 3; s.lph = 1;
+    s.pbw = 8; s.pbh = 2; s.pbt = s.tt + 2;
+  } else {
+    return s;
+  }
+  s.patch_rows = s.pbw * s.pbh * s.pbt;
+  if (conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, g.cout_pad()) > kSmemLimit) return s;
+  // ragged tiles are legal (stores are masked) but waste tensor work; require a reasonable fit
+  const double eff = (double)g.Wo * g.Ho * g.To /
+                     ((double)ceil_div(g.Wo, s.tw) * ceil_div(g.Ho, s.th) * ceil_div(g.To, s.tt) * 128);
+  if (eff < 0.6) return s;
+  s.ok = true;
+  return s;
+}
+}  // namespace
+
+bool conv_patch_applicable(const ConvGeom& g) { return patch_shape(g).ok; }
+
+bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
+                             const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
+                             const __nv_bfloat16* residual, bool relu, ConvPatchParams* out,
+                             std::string* err) {
+  const PatchShape s = patch_shape(g);
+  if (!s.ok) {
+    if (err) *err = "conv_patch: geometry not supported";
+    return false;
+  }
+  ConvPatchParams& p = *out;
+  memset(&p, 0, sizeof p);
+  const int cp = g.cin_pad(), np = g.cout_pad();
+  p.shift = shift;
+  p.residual = residual;
+  p.y = y;
+  p.nkb = s.nkb;
+  p.cin_pad = cp;
+  p.patch_rows = s.patch_rows;
+  p.num_taps = s.taps;
+  p.n = np;
+  p.tw = s.tw; p.th = s.th; p.tt = s.tt;
+  p.lpw = s.lpw; p.lph = s.lph;
+  p.tiles_w = ceil_div(g.Wo, s.tw);
+  p.tiles_h = ceil_div(g.Ho, s.th);
+  p.tiles_t = ceil_div(g.To, s.tt);
+  p.tiles_b = B;
+  p.aw = s.spatial ? -1 : 0;
+  p.ah = s.spatial ? -1 : 0;
+  p.at = s.spatial ? 0 : -1;
+  p.Wo = g.Wo; p.Ho = g.Ho; p.To = g.To; p.B = B;
+  p.cout_pad = np;
+  p.relu = relu ? 1 : 0;
+  for (int tap = 0; tap < s.taps; ++tap)
+    p.tap_shift[tap] = (int16_t)(s.spatial ? (tap / 3) * s.pbw + (tap % 3) : tap * s.pbw * s.pbh);
+  {
+    const uint64_t dims[5] = {(uint64_t)cp, (uint64_t)g.Wi, (uint64_t)g.Hi, (uint64_t)g.Ti, (uint64_t)B};
+    const uint64_t strides[4] = {(uint64_t)cp * 2, (uint64_t)g.Wi * cp * 2,
+                                 (uint64_t)g.Hi * g.Wi * cp * 2, (uint64_t)g.Ti * g.Hi * g.Wi * cp * 2};
+    const uint32_t box[5] = {64u, (uint32_t)s.pbw, (uint32_t)s.pbh, (uint32_t)s.pbt, 1u};
+    if (!encode_bf16(&p.a_map, x, 5, dims, strides, box, 128, err)) return false;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)np};
+    const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
+    const uint32_t box[2] = {64u, (uint32_t)np};
+    if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, 128, err)) return false;
   }
   return true;
 }

@@ -4,6 +4,7 @@
 #include <string>
 #include <vector>
 
+#include "conv_patch.cuh"
 #include "conv_tc.cuh"
 
 namespace rnb {
@@ -35,8 +36,10 @@ struct ConvGeom {
   }
 };
 
-// torch weight (cout, cin, kt, kh, kw) fp32 -> K-major bf16 rows (cout_pad, k_total)
-void pack_conv_weights_tc(const ConvGeom& g, const float* w, std::vector<uint16_t>* packed);
+// torch weight (cout, cin, kt, kh, kw) fp32 -> K-major bf16 rows (cout_pad, k_total); row n is
+// multiplied by scale[n] (the folded BatchNorm scale) before rounding when `scale` is given
+void pack_conv_weights_tc(const ConvGeom& g, const float* w, const float* scale,
+                          std::vector<uint16_t>* packed);
 
 // torch weight (cout, cin, kt, kh, kw) -> (kt, kh, kw, cin, cout) fp32 for the direct convolution
 void pack_conv_weights_ref(const ConvGeom& g, const float* w, std::vector<float>* packed);
@@ -44,9 +47,16 @@ void pack_conv_weights_ref(const ConvGeom& g, const float* w, std::vector<float>
 // Fill `out` for a batch of B clips.  All pointers are device pointers.  Returns false and sets
 // *err on failure (unsupported geometry or a tensor-map encoding error).
 bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
-                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* scale,
-                          const float* shift, const __nv_bfloat16* residual, bool relu, int num_sms,
+                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift, const __nv_bfloat16* residual, bool relu, int num_sms,
                           ConvTcParams* out, std::string* err);
+
+// Patch kernel (conv_patch.cuh): applicable to stride-1 1x3x3 and 3x1x1 convolutions whose packed
+// weights fit in shared memory next to two activation patches.
+bool conv_patch_applicable(const ConvGeom& g);
+bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
+                             const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
+                             const __nv_bfloat16* residual, bool relu, ConvPatchParams* out,
+                             std::string* err);
 
 uint16_t f32_to_bf16_bits(float f);
 float bf16_bits_to_f32(uint16_t b);

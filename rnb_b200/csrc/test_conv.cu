@@ -79,7 +79,7 @@ static bool run_case(const Case& c, int perf_iters) {
       for (int ch = 0; ch < g.cout; ++ch) rb[i * np + ch] = f32_to_bf16_bits(res[i * g.cout + ch]);
   }
   std::vector<uint16_t> wp;
-  pack_conv_weights_tc(g, w.data(), &wp);
+  pack_conv_weights_tc(g, w.data(), scale.data(), &wp);
   std::vector<float> wr;
   pack_conv_weights_ref(g, w.data(), &wr);
 
@@ -117,7 +117,7 @@ static bool run_case(const Case& c, int perf_iters) {
 
   ConvTcParams tp;
   std::string err;
-  if (!build_conv_tc_params(g, B, dxb, dwp, dyb, dscale, dshift, drb, c.relu, num_sms, &tp, &err)) {
+  if (!build_conv_tc_params(g, B, dxb, dwp, dyb, dshift, drb, c.relu, num_sms, &tp, &err)) {
     printf("%-28s PLAN FAILED: %s\n", c.name, err.c_str());
     return false;
   }
@@ -154,6 +154,71 @@ static bool run_case(const Case& c, int perf_iters) {
          c.name, B, bw, bh, bt, 128 / (bw * bh * bt), tp.n_tiles, tp.block_n, tp.num_stages,
          tp.num_taps, max_ref, max_err, rel, bad_pad, worst, pass ? "PASS" : "FAIL");
 
+  // ---- the patch kernel on the same problem, with both descriptor base-offset conventions
+  bool patch_pass = true;
+  if (conv_patch_applicable(g)) {
+    patch_pass = false;
+    for (int mode = 0; mode < 1; ++mode) {
+      ConvPatchParams pp;
+      if (!build_conv_patch_params(g, B, dxb, dwp, dyb, dshift, drb, c.relu, &pp, &err)) {
+        printf("    patch PLAN FAILED: %s\n", err.c_str());
+        break;
+      }
+      CK(cudaMemset(dyb, 0xff, out_pos * np * 2));
+      CK(launch_conv_patch(pp, num_sms, 0));
+      CK(cudaDeviceSynchronize());
+      CK(cudaMemcpy(yb.data(), dyb, yb.size() * 2, cudaMemcpyDeviceToHost));
+      double perr = 0;
+      size_t pbad = 0, nanc = 0;
+      for (size_t i = 0; i < out_pos; ++i)
+        for (int ch = 0; ch < np; ++ch) {
+          const float t = bf16_bits_to_f32(yb[i * np + ch]);
+          if (ch >= g.cout) {
+            if (t != 0.f) ++pbad;
+            continue;
+          }
+          const double e = fabs((double)t - yr[i * g.cout + ch]);
+          if (!(e == e)) ++nanc;
+          if (!(e <= perr)) perr = e;
+        }
+      const bool ok = perr / (max_ref > 0 ? max_ref : 1) < 1e-2 && pbad == 0 && nanc == 0;
+      printf("    patch kernel: max|err|=%.4f pad_bad=%zu nan=%zu  %s\n", perr, pbad, nanc,
+             ok ? "PASS" : "FAIL");
+      if (ok && perf_iters > 0 && mode == 0) {
+        long long* ddbg;
+        CK(cudaMalloc(&ddbg, 148 * 8 * 8));
+        CK(cudaMemset(ddbg, 0, 148 * 8 * 8));
+        pp.dbg = ddbg;
+        CK(launch_conv_patch(pp, num_sms, 0));
+        CK(cudaDeviceSynchronize());
+        long long h[148 * 8];
+        CK(cudaMemcpy(h, ddbg, sizeof h, cudaMemcpyDeviceToHost));
+        pp.dbg = nullptr;
+        cudaFree(ddbg);
+        for (int b : {0, 73, 147})
+          printf("    cta %3d: tiles %lld | producer wait p_empty %lld | mma wait weights %lld, tmem_empty %lld, "
+                 "p_full %lld, total %lld | epi wait tmem_full %lld, total %lld (cycles)\n",
+                 b, h[b * 8 + 5], h[b * 8 + 0], h[b * 8 + 1], h[b * 8 + 2], h[b * 8 + 3], h[b * 8 + 4],
+                 h[b * 8 + 6], h[b * 8 + 7]);
+      }
+      if (ok && perf_iters > 0) {
+        cudaEvent_t e0, e1;
+        CK(cudaEventCreate(&e0));
+        CK(cudaEventCreate(&e1));
+        for (int i = 0; i < 3; ++i) CK(launch_conv_patch(pp, num_sms, 0));
+        CK(cudaEventRecord(e0));
+        for (int i = 0; i < perf_iters; ++i) CK(launch_conv_patch(pp, num_sms, 0));
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        const double us = ms * 1e3 / perf_iters;
+        printf("    patch perf: %.1f us  %.1f TFLOP/s\n", us, g.flops(B) / us * 1e-6);
+      }
+      patch_pass = patch_pass || ok;
+    }
+  }
+
   if (perf_iters > 0 && pass) {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
@@ -175,7 +240,7 @@ static bool run_case(const Case& c, int perf_iters) {
   cudaFree(dwp); cudaFree(dyb);
   if (dres) cudaFree(dres);
   if (drb) cudaFree(drb);
-  return pass;
+  return pass && patch_pass;
 }
 
 // stem: uint8 frames -> unfolded rows -> tcgen05, against uint8 -> fp32 NDHWC -> direct conv
@@ -197,7 +262,7 @@ static bool run_stem(int B) {
     shift[n] = 0.2f * frand();
   }
   std::vector<uint16_t> wp;
-  pack_conv_weights_tc(gu, w.data(), &wp);
+  pack_conv_weights_tc(gu, w.data(), scale.data(), &wp);
   std::vector<float> wr;
   pack_conv_weights_ref(g, w.data(), &wr);
   uint8_t* dframes;
@@ -229,7 +294,7 @@ static bool run_stem(int B) {
   CK(launch_conv_ref(rp, 0));
   ConvTcParams tp;
   std::string err;
-  if (!build_conv_tc_params(gu, B, du, dwp, dyb, dscale, dshift, nullptr, true, num_sms, &tp, &err)) {
+  if (!build_conv_tc_params(gu, B, du, dwp, dyb, dshift, nullptr, true, num_sms, &tp, &err)) {
     printf("stem spatial PLAN FAILED: %s\n", err.c_str());
     return false;
   }
