@@ -70,6 +70,15 @@ int rnb_r2p1d_finalize(void* handle);
 int rnb_r2p1d_forward(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
                       void* stream);
 
+/* Forward pass plus the per-video reduction of the aggregator step, for a handle ending at layer 5:
+ * sum[j] = sum over the `batch` clips of logits[b][j] and cls = argmax_j sum[j] (lowest index on
+ * ties), produced on the GPU by the classifier kernel itself.  logits (batch x num_classes) and sum
+ * (num_classes) may be NULL.  Replaces R2P1DAggregator's tensor.cpu().numpy().sum(axis=0) and
+ * .argmax() (models/r2p1d/model.py:254,259) when runner and aggregator share a GPU, so that one
+ * int instead of (n, 400) floats crosses to the host. */
+int rnb_r2p1d_classify(void* handle, const void* in, int in_fmt, int batch, float* logits,
+                       float* sum, int* cls, void* stream);
+
 /* Per-clip logical shape (C, T, H, W) of the handle's input (which = 0) or output (which = 1);
  * for a model ending at layer 5 the output is (num_classes, 1, 1, 1).  Mirrors
  * R2P1DRunner.input_dict at models/r2p1d/model.py:29-33. */
@@ -103,6 +112,19 @@ void rnb_r2p1d_destroy(void* handle);
  * the reference behaviour). */
 int rnb_preprocess_u8(const uint8_t* in, int batch, const float* scale3, const float* bias3,
                       void* out, int out_fmt, void* stream);
+
+/* The classifier tail of the network as one launch: global average pool over `positions` (the
+ * AdaptiveAvgPool3d(1) of models/r2p1d/network.py:35), Linear(channels -> classes)
+ * (network.py:56,60), and the aggregator's sum over clips + arg-max (models/r2p1d/model.py:254,259).
+ * x: bf16 (batch, positions, channels) channels-last activations of the last stage; w: fp32
+ * (classes, channels); bias: fp32 (classes).  logits / sum / cls may each be NULL.
+ * `scratch` is device memory of at least rnb_pool_fc_classify_scratch_bytes(batch, classes) bytes,
+ * 256-byte aligned, owned by the caller; its contents on entry do not matter and two calls that may
+ * overlap on the GPU must not share it. */
+size_t rnb_pool_fc_classify_scratch_bytes(int batch, int classes);
+int rnb_pool_fc_classify(const void* x, int batch, int positions, int channels, const float* w,
+                         const float* bias, int classes, float* logits, float* sum, int* cls,
+                         void* scratch, size_t scratch_bytes, void* stream);
 
 /* Concatenate k row-blocks (rows[i] rows of row_bytes bytes each, device pointers in the HOST
  * array srcs) into dst.  Replaces torch.cat(self.stacked_tensors, dim=0) at batcher.py:28. */

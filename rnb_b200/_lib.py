@@ -33,6 +33,15 @@ PROTOTYPES = {
     'rnb_r2p1d_forward': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                          ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                          ctypes.c_void_p]),
+    'rnb_r2p1d_classify': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                          ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                          ctypes.c_void_p, ctypes.c_void_p]),
+    'rnb_pool_fc_classify_scratch_bytes': (ctypes.c_size_t, [ctypes.c_int, ctypes.c_int]),
+    'rnb_pool_fc_classify': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                            ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                            ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                            ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t,
+                                            ctypes.c_void_p]),
     'rnb_r2p1d_profile': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                          ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                          ctypes.c_void_p, _c_f32_p, ctypes.c_int]),

@@ -99,6 +99,46 @@ int rnb_r2p1d_forward(void* handle, const void* in, int in_fmt, int batch, void*
   return RNB_OK;
 }
 
+int rnb_r2p1d_classify(void* handle, const void* in, int in_fmt, int batch, float* logits,
+                       float* sum, int* cls, void* stream) {
+  if (!handle) return fail(RNB_EINVAL, "handle is NULL");
+  if (batch < 1) return fail(RNB_EINVAL, "rnb_r2p1d_classify needs at least one clip");
+  std::string err;
+  const int rc = static_cast<rnb::R2P1DModel*>(handle)->forward(
+      in, in_fmt, batch, logits, RNB_FMT_F32_LOGITS, static_cast<cudaStream_t>(stream), &err,
+      nullptr, sum, cls, true);
+  if (rc != RNB_OK) {
+    (void)cudaGetLastError();
+    return fail(rc, err);
+  }
+  return RNB_OK;
+}
+
+size_t rnb_pool_fc_classify_scratch_bytes(int batch, int classes) {
+  if (batch < 0 || classes < 0) return 0;
+  return rnb::pool_fc_classify_scratch_bytes(batch, classes);
+}
+
+int rnb_pool_fc_classify(const void* x, int batch, int positions, int channels, const float* w,
+                         const float* bias, int classes, float* logits, float* sum, int* cls,
+                         void* scratch, size_t scratch_bytes, void* stream) {
+  if (batch < 0 || positions < 1 || classes < 1 || channels < 8 || channels % 8 != 0)
+    return fail(RNB_EINVAL, "rnb_pool_fc_classify: bad shape (channels must be a multiple of 8)");
+  if (batch == 0) return RNB_OK;
+  if (!x || !w || !bias || !scratch) return fail(RNB_EINVAL, "null pointer");
+  if (scratch_bytes < rnb::pool_fc_classify_scratch_bytes(batch, classes))
+    return fail(RNB_EINVAL, "rnb_pool_fc_classify: scratch buffer too small, need " +
+                                std::to_string(rnb::pool_fc_classify_scratch_bytes(batch, classes)) +
+                                " bytes");
+  if (reinterpret_cast<uintptr_t>(scratch) % 256 != 0)
+    return fail(RNB_EINVAL, "rnb_pool_fc_classify: scratch must be 256-byte aligned");
+  cudaError_t e = rnb::launch_pool_fc_classify_bf16(
+      static_cast<const __nv_bfloat16*>(x), batch, positions, channels, w, bias, classes, logits, sum,
+      cls, scratch, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return cuda_fail(e, "rnb_pool_fc_classify");
+  return RNB_OK;
+}
+
 int rnb_r2p1d_profile(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
                       void* stream, float* ms, int cap) {
   if (!handle) return fail(RNB_EINVAL, "handle is NULL");

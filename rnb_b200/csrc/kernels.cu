@@ -76,44 +76,65 @@ __global__ void conv_ref_kernel(const ConvRefParams p) {
 }
 
 // ------------------------------------------------------------------------------ preprocessing
-// One thread writes one 16-byte chunk: 2 input columns x 4 channel slots of an unfolded stem row.
+// Unfolded stem rows.  A CTA stages kStemRows image rows (3 channels x 112 pixels each, read with
+// coalesced 4-pixel loads) in shared memory with a 4-pixel zero margin on both sides, then every
+// thread assembles 16-byte output chunks (2 input columns x 4 channel slots) and stores them
+// coalesced: 336 bytes in, 3584 bytes out per image row.
+constexpr int kStemRows = 8;
+constexpr int kStemPitch = kClipW + 8;  // 4 zero pixels | 112 pixels | 4 zero pixels
+
 template <typename In>
-__global__ void to_stem_kernel(const In* __restrict__ in, long long chunks, Affine3 aff,
-                               uint4* __restrict__ out, bool ncdhw) {
-  for (long long o = blockIdx.x * (long long)blockDim.x + threadIdx.x; o < chunks;
-       o += (long long)gridDim.x * blockDim.x) {
-    const int cp = (int)(o & 3);
-    long long r = o >> 2;
-    const int wo = (int)(r % (kClipW / 2));
-    r /= (kClipW / 2);
-    const int h = (int)(r % kClipH);
-    r /= kClipH;
-    const int t = (int)(r % kClipT);
-    const long long b = r / kClipT;
-    float v[2][3];
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int col = cp * 2 + j;
-      const int w = 2 * wo + col - 3;
-      const bool ok = (col < 7) && (w >= 0) && (w < kClipW);
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        float x = 0.f;
-        if (ok) {
-          // uint8 frames are (B, T, C, H, W); fp32 tensors are (B, C, T, H, W)
-          const long long idx = ncdhw ? ((((b * kClipC + c) * kClipT + t) * kClipH + h) * kClipW + w)
-                                      : ((((b * kClipT + t) * kClipC + c) * kClipH + h) * kClipW + w);
-          x = fmaf((float)in[idx], aff.s[c], aff.b[c]);
-        }
-        v[j][c] = x;
-      }
+__global__ void __launch_bounds__(256)
+to_stem_kernel(const In* __restrict__ in, int total_rows, Affine3 aff, uint4* __restrict__ out,
+               bool ncdhw) {
+  __shared__ float px[kStemRows][kClipC][kStemPitch];
+  const int row0 = blockIdx.x * kStemRows;
+  for (int i = threadIdx.x; i < kStemRows * kClipC * 8; i += blockDim.x) {
+    const int r = i / (kClipC * 8), c = (i / 8) % kClipC, m = i % 8;
+    px[r][c][m < 4 ? m : kClipW + m] = 0.f;
+  }
+  // one thread loads 4 consecutive pixels of one (row, channel)
+  for (int i = threadIdx.x; i < kStemRows * kClipC * (kClipW / 4); i += blockDim.x) {
+    const int q = i % (kClipW / 4);
+    const int c = (i / (kClipW / 4)) % kClipC;
+    const int r = i / (kClipC * (kClipW / 4));
+    const int row = row0 + r;  // row = (b * T + t) * H + h
+    if (row >= total_rows) continue;
+    const int h = row % kClipH;
+    const int bt = row / kClipH;
+    const int t = bt % kClipT;
+    const long long b = bt / kClipT;
+    // uint8 frames are (B, T, C, H, W); fp32 tensors are (B, C, T, H, W)
+    const long long base = ncdhw ? ((((b * kClipC + c) * kClipT + t) * kClipH + h) * (long long)kClipW)
+                                 : ((((b * kClipT + t) * kClipC + c) * kClipH + h) * (long long)kClipW);
+    float v[4];
+    if (sizeof(In) == 1) {
+      const uchar4 u = *reinterpret_cast<const uchar4*>(in + base + 4 * q);
+      v[0] = u.x; v[1] = u.y; v[2] = u.z; v[3] = u.w;
+    } else {
+      const float4 f = *reinterpret_cast<const float4*>(in + base + 4 * q);
+      v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
     }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) px[r][c][4 + 4 * q + j] = fmaf(v[j], aff.s[c], aff.b[c]);
+  }
+  __syncthreads();
+  constexpr int kChunksPerRow = (kClipW / 2) * 4;  // 56 output positions x 4 chunks
+  for (int i = threadIdx.x; i < kStemRows * kChunksPerRow; i += blockDim.x) {
+    const int r = i / kChunksPerRow, o = i % kChunksPerRow;
+    const int row = row0 + r;
+    if (row >= total_rows) continue;
+    const int wo = o >> 2, cp = o & 3;
+    // columns 2*cp and 2*cp+1 of the 8-wide window that starts at input pixel 2*wo - 3;
+    // window column 7 carries zero weights and is stored as zero
+    const int w0 = 2 * wo - 3 + 2 * cp + 4;  // index into the padded row
+    const bool second = (2 * cp + 1) < 7;
     uint4 q;
-    q.x = pack2(v[0][0], v[0][1]);
-    q.y = pack2(v[0][2], 0.f);
-    q.z = pack2(v[1][0], v[1][1]);
-    q.w = pack2(v[1][2], 0.f);
-    out[o] = q;
+    q.x = pack2(px[r][0][w0], px[r][1][w0]);
+    q.y = pack2(px[r][2][w0], 0.f);
+    q.z = second ? pack2(px[r][0][w0 + 1], px[r][1][w0 + 1]) : 0u;
+    q.w = second ? pack2(px[r][2][w0 + 1], 0.f) : 0u;
+    out[(long long)row * kChunksPerRow + o] = q;
   }
 }
 
@@ -196,20 +217,35 @@ __global__ void bsc_to_bcs_kernel(const In* __restrict__ in, int C, int S, int c
 }
 
 // ------------------------------------------------------------------------------ pool + FC
-// grid (B, class_chunks); every CTA pools its clip (S x C, coalesced over channels) into shared
-// memory, then each warp produces classes with lane-strided dot products and a shuffle reduction.
+// grid (B, class_chunks), 256 threads.  Pooling: thread t owns channel pair (2t, 2t+1) (+512, ...)
+// and sums the S positions with coalesced 4-byte (bf16) / 8-byte (fp32) loads, S loads in flight.
+// Classifier: each warp takes classes of the chunk, lanes stride the C weights with 16-byte loads,
+// shuffle reduction.
 template <typename In>
-__global__ void pool_fc_kernel(const In* __restrict__ x, int S, int C, const float* __restrict__ w,
-                               const float* __restrict__ bias, int num_classes,
-                               float* __restrict__ logits) {
-  extern __shared__ float pooled[];
+__device__ __forceinline__ void pool_fc_body(const In* __restrict__ x, int S, int C,
+                                             const float* __restrict__ w,
+                                             const float* __restrict__ bias, int num_classes,
+                                             float* __restrict__ logits, float* __restrict__ logits2,
+                                             float* pooled) {
   const int b = blockIdx.x;
   const In* xb = x + (long long)b * S * C;
   const float inv = 1.f / (float)S;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    float acc = 0.f;
-    for (int s = 0; s < S; ++s) acc += (float)xb[(long long)s * C + c];
-    pooled[c] = acc * inv;
+  for (int c = 2 * threadIdx.x; c < C; c += 2 * blockDim.x) {
+    float a0 = 0.f, a1 = 0.f;
+#pragma unroll 7
+    for (int s = 0; s < S; ++s) {
+      if (sizeof(In) == 2) {
+        const uint32_t u = *reinterpret_cast<const uint32_t*>(xb + (long long)s * C + c);
+        a0 += __uint_as_float(u << 16);
+        a1 += __uint_as_float(u & 0xffff0000u);
+      } else {
+        const float2 f = *reinterpret_cast<const float2*>(xb + (long long)s * C + c);
+        a0 += f.x;
+        a1 += f.y;
+      }
+    }
+    pooled[c] = a0 * inv;
+    pooled[c + 1] = a1 * inv;
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -217,12 +253,90 @@ __global__ void pool_fc_kernel(const In* __restrict__ x, int S, int C, const flo
   const int j0 = blockIdx.y * per_chunk;
   const int j1 = min(num_classes, j0 + per_chunk);
   for (int j = j0 + warp; j < j1; j += nwarps) {
-    const float* wj = w + (long long)j * C;
+    const float4* wj = reinterpret_cast<const float4*>(w + (long long)j * C);
     float acc = 0.f;
-    for (int c = lane; c < C; c += 32) acc = fmaf(pooled[c], __ldg(wj + c), acc);
+    for (int c4 = lane; c4 < C / 4; c4 += 32) {
+      const float4 wv = __ldg(wj + c4);
+      const float4 pv = *reinterpret_cast<const float4*>(pooled + 4 * c4);
+      acc = fmaf(pv.x, wv.x, acc);
+      acc = fmaf(pv.y, wv.y, acc);
+      acc = fmaf(pv.z, wv.z, acc);
+      acc = fmaf(pv.w, wv.w, acc);
+    }
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
-    if (lane == 0) logits[(long long)b * num_classes + j] = acc + bias[j];
+    if (lane == 0) {
+      const float v = acc + bias[j];
+      if (logits) logits[(long long)b * num_classes + j] = v;
+      if (logits2) logits2[(long long)b * num_classes + j] = v;
+    }
+  }
+}
+
+template <typename In>
+__global__ void __launch_bounds__(256)
+pool_fc_kernel(const In* __restrict__ x, int S, int C, const float* __restrict__ w,
+               const float* __restrict__ bias, int num_classes, float* __restrict__ logits) {
+  extern __shared__ float pooled[];
+  pool_fc_body<In>(x, S, C, w, bias, num_classes, logits, nullptr, pooled);
+}
+
+// pool + classifier + per-video reduction in one launch.  Every CTA writes its slice of the per-clip
+// logits to `staged` (scratch) and takes a ticket from `counter` (scratch, zero on entry); the CTA
+// that draws the last ticket sums the clips in a fixed order (deterministic, unlike atomics on the
+// sums), picks the arg-max with numpy's lowest-index tie rule, and re-arms the counter.
+template <typename In>
+__global__ void __launch_bounds__(256)
+pool_fc_classify_kernel(const In* __restrict__ x, int S, int C, const float* __restrict__ w,
+                        const float* __restrict__ bias, int num_classes,
+                        float* __restrict__ logits, float* __restrict__ sum, int* __restrict__ cls,
+                        float* __restrict__ staged, unsigned int* __restrict__ counter) {
+  extern __shared__ float pooled[];
+  __shared__ unsigned int ticket;
+  __shared__ float best_v[8];
+  __shared__ int best_i[8];
+  pool_fc_body<In>(x, S, C, w, bias, num_classes, staged, logits, pooled);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) ticket = atomicAdd(counter, 1u);
+  __syncthreads();
+  if (ticket != gridDim.x * gridDim.y - 1) return;
+  __threadfence();
+  const int B = gridDim.x;
+  float bv = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int j = threadIdx.x; j < num_classes; j += blockDim.x) {
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc += __ldcg(staged + (long long)b * num_classes + j);
+    if (sum) sum[j] = acc;
+    if (acc > bv || (acc == bv && j < bi)) {
+      bv = acc;
+      bi = j;
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, off);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+    if (ov > bv || (ov == bv && oi < bi)) {
+      bv = ov;
+      bi = oi;
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    best_v[warp] = bv;
+    best_i[warp] = bi;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int k = 1; k < (int)(blockDim.x >> 5); ++k)
+      if (best_v[k] > bv || (best_v[k] == bv && best_i[k] < bi)) {
+        bv = best_v[k];
+        bi = best_i[k];
+      }
+    if (cls) *cls = bi;
+    *counter = 0u;  // ready for the next launch on this scratch buffer
   }
 }
 
@@ -304,19 +418,19 @@ cudaError_t launch_conv_ref(const ConvRefParams& p, cudaStream_t stream) {
 
 cudaError_t launch_pre_u8_to_stem(const uint8_t* in, int batch, const float* scale3,
                                   const float* bias3, __nv_bfloat16* out, cudaStream_t s) {
-  const long long chunks = (long long)batch * kClipT * kClipH * (kClipW / 2) * 4;
-  if (chunks == 0) return cudaSuccess;
-  to_stem_kernel<uint8_t><<<blocks_for(chunks), kThreads, 0, s>>>(
-      in, chunks, make_affine(scale3, bias3), reinterpret_cast<uint4*>(out), false);
+  const int rows = batch * kClipT * kClipH;
+  if (rows == 0) return cudaSuccess;
+  to_stem_kernel<uint8_t><<<(rows + kStemRows - 1) / kStemRows, 256, 0, s>>>(
+      in, rows, make_affine(scale3, bias3), reinterpret_cast<uint4*>(out), false);
   return cudaGetLastError();
 }
 
 cudaError_t launch_f32_ncdhw_to_stem(const float* in, int batch, __nv_bfloat16* out,
                                      cudaStream_t s) {
-  const long long chunks = (long long)batch * kClipT * kClipH * (kClipW / 2) * 4;
-  if (chunks == 0) return cudaSuccess;
-  to_stem_kernel<float><<<blocks_for(chunks), kThreads, 0, s>>>(
-      in, chunks, make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
+  const int rows = batch * kClipT * kClipH;
+  if (rows == 0) return cudaSuccess;
+  to_stem_kernel<float><<<(rows + kStemRows - 1) / kStemRows, 256, 0, s>>>(
+      in, rows, make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
   return cudaGetLastError();
 }
 
@@ -388,15 +502,33 @@ cudaError_t launch_pool_fc_bf16(const __nv_bfloat16* x, int B, int S, int C, con
                                 const float* bias, int num_classes, float* logits,
                                 cudaStream_t s) {
   if (B == 0) return cudaSuccess;
-  pool_fc_kernel<__nv_bfloat16><<<dim3(B, 4), 256, C * sizeof(float), s>>>(x, S, C, w, bias,
+  pool_fc_kernel<__nv_bfloat16><<<dim3(B, 10), 256, C * sizeof(float), s>>>(x, S, C, w, bias,
                                                                           num_classes, logits);
   return cudaGetLastError();
 }
 cudaError_t launch_pool_fc_f32(const float* x, int B, int S, int C, const float* w,
                                const float* bias, int num_classes, float* logits, cudaStream_t s) {
   if (B == 0) return cudaSuccess;
-  pool_fc_kernel<float><<<dim3(B, 4), 256, C * sizeof(float), s>>>(x, S, C, w, bias, num_classes,
+  pool_fc_kernel<float><<<dim3(B, 10), 256, C * sizeof(float), s>>>(x, S, C, w, bias, num_classes,
                                                                   logits);
+  return cudaGetLastError();
+}
+
+size_t pool_fc_classify_scratch_bytes(int batch, int num_classes) {
+  return 256 + (size_t)batch * (size_t)num_classes * sizeof(float);
+}
+
+cudaError_t launch_pool_fc_classify_bf16(const __nv_bfloat16* x, int B, int S, int C, const float* w,
+                                         const float* bias, int num_classes, float* logits,
+                                         float* sum, int* cls, void* scratch, cudaStream_t s) {
+  if (B == 0) return cudaSuccess;
+  // the counter must be zero on entry whatever the previous user of the scratch left behind
+  cudaError_t e = cudaMemsetAsync(scratch, 0, 256, s);
+  if (e != cudaSuccess) return e;
+  unsigned int* counter = static_cast<unsigned int*>(scratch);
+  float* staged = reinterpret_cast<float*>(static_cast<char*>(scratch) + 256);
+  pool_fc_classify_kernel<__nv_bfloat16><<<dim3(B, 10), 256, C * sizeof(float), s>>>(
+      x, S, C, w, bias, num_classes, logits, sum, cls, staged, counter);
   return cudaGetLastError();
 }
 

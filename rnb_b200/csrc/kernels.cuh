@@ -61,6 +61,14 @@ cudaError_t launch_pool_fc_bf16(const __nv_bfloat16* x, int B, int S, int C, con
 cudaError_t launch_pool_fc_f32(const float* x, int B, int S, int C, const float* w,
                                const float* bias, int num_classes, float* logits, cudaStream_t s);
 
+// Same plus the per-video reduction (sum over the B clips, arg-max) in one launch.  `scratch` is a
+// device buffer of pool_fc_classify_scratch_bytes(B, num_classes) bytes, 256-byte aligned; its
+// contents on entry do not matter.  logits / sum / cls may each be nullptr.
+size_t pool_fc_classify_scratch_bytes(int batch, int num_classes);
+cudaError_t launch_pool_fc_classify_bf16(const __nv_bfloat16* x, int B, int S, int C, const float* w,
+                                         const float* bias, int num_classes, float* logits,
+                                         float* sum, int* cls, void* scratch, cudaStream_t s);
+
 // ---- batching / aggregation ----------------------------------------------------------------------
 constexpr int kMaxGatherSrcs = 64;
 cudaError_t launch_batch_gather(const void* const* srcs, const int* rows, int k, void* dst,

@@ -65,6 +65,8 @@ void R2P1DModel::release() {
     if (s) cudaFree(s);
     s = nullptr;
   }
+  if (d_classify_scratch_) cudaFree(d_classify_scratch_);
+  d_classify_scratch_ = nullptr;
   if (d_fc_w_) cudaFree(d_fc_w_);
   if (d_fc_b_) cudaFree(d_fc_b_);
   d_fc_w_ = d_fc_b_ = nullptr;
@@ -293,7 +295,10 @@ int R2P1DModel::finalize(std::string* err) {
       release();
       return RNB_EPARAM;
     }
-    bool ok = cuda_ok(cudaMalloc(&d_fc_w_, w->data.size() * 4), "cudaMalloc", err) &&
+    bool ok = cuda_ok(cudaMalloc(&d_classify_scratch_,
+                                 pool_fc_classify_scratch_bytes(max_batch_, num_classes_)),
+                      "cudaMalloc(classifier scratch)", err) &&
+              cuda_ok(cudaMalloc(&d_fc_w_, w->data.size() * 4), "cudaMalloc", err) &&
               cuda_ok(cudaMalloc(&d_fc_b_, b->data.size() * 4), "cudaMalloc", err) &&
               cuda_ok(cudaMemcpy(d_fc_w_, w->data.data(), w->data.size() * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err) &&
               cuda_ok(cudaMemcpy(d_fc_b_, b->data.data(), b->data.size() * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err);
@@ -376,7 +381,8 @@ int R2P1DModel::profile(const void* in, int in_fmt, int batch, void* out, int ou
 }
 
 int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int out_fmt,
-                        cudaStream_t stream, std::string* err, cudaEvent_t* events) {
+                        cudaStream_t stream, std::string* err, cudaEvent_t* events,
+                        float* video_sum, int* video_cls, bool video) {
   int ev_idx = 0;
   auto mark = [&]() {
     if (events) cudaEventRecord(events[ev_idx++], stream);
@@ -392,8 +398,12 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
     return RNB_EINVAL;
   }
   if (batch == 0) return RNB_OK;
-  if (in == nullptr || out == nullptr) {
+  if (in == nullptr || (out == nullptr && !video)) {
     if (err) *err = "null input or output pointer";
+    return RNB_EINVAL;
+  }
+  if (video && end_idx_ != 5) {
+    if (err) *err = "per-video classification needs a model that ends at layer 5";
     return RNB_EINVAL;
   }
   const bool tc = dtype_ == RNB_DTYPE_BF16;
@@ -497,7 +507,18 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
 
   // ---- output
   const int S_out = out_dims_.T * out_dims_.H * out_dims_.W;
-  if (end_idx_ == 5) {
+  if (end_idx_ == 5 && video && tc) {
+    e = launch_pool_fc_classify_bf16((const __nv_bfloat16*)slots_[final_slot_], batch, S_out, 512,
+                                     d_fc_w_, d_fc_b_, num_classes_, (float*)out, video_sum,
+                                     video_cls, d_classify_scratch_, stream);
+  } else if (end_idx_ == 5 && video) {
+    // fp32 parity mode: separate classifier and reduction kernels, logits staged in the scratch
+    float* lg = out ? (float*)out : reinterpret_cast<float*>((char*)d_classify_scratch_ + 256);
+    e = launch_pool_fc_f32((const float*)slots_[final_slot_], batch, S_out, 512, d_fc_w_, d_fc_b_,
+                           num_classes_, lg, stream);
+    if (e == cudaSuccess)
+      e = launch_logits_sum_argmax(lg, batch, num_classes_, video_sum, video_cls, stream);
+  } else if (end_idx_ == 5) {
     e = tc ? launch_pool_fc_bf16((const __nv_bfloat16*)slots_[final_slot_], batch, S_out, 512,
                                  d_fc_w_, d_fc_b_, num_classes_, (float*)out, stream)
            : launch_pool_fc_f32((const float*)slots_[final_slot_], batch, S_out, 512, d_fc_w_,

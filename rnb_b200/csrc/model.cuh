@@ -42,7 +42,8 @@ class R2P1DModel {
   int finalize(std::string* err);  // RNB_* code
   // `events`, when given, receives num_launches()+1 events recorded around every kernel
   int forward(const void* in, int in_fmt, int batch, void* out, int out_fmt, cudaStream_t stream,
-              std::string* err, cudaEvent_t* events = nullptr);
+              std::string* err, cudaEvent_t* events = nullptr, float* video_sum = nullptr,
+              int* video_cls = nullptr, bool video = false);
   int profile(const void* in, int in_fmt, int batch, void* out, int out_fmt, cudaStream_t stream,
               float* ms, int cap, std::string* err);
   bool op_info(int op, std::string* name, double* flops_per_clip, double* act_bytes_per_clip,
@@ -78,6 +79,7 @@ class R2P1DModel {
   int final_slot_ = SLOT_X;
   void* slots_[NUM_SLOTS] = {};
   size_t slot_elems_per_clip_[NUM_SLOTS] = {};
+  void* d_classify_scratch_ = nullptr;  // staged logits + arrival counter of the fused classifier
   float* d_fc_w_ = nullptr;
   float* d_fc_b_ = nullptr;
   // tensor-core launch plan of one convolution for one batch size: the patch kernel where it

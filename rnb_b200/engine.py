@@ -237,3 +237,26 @@ class R2P1DEngine:
         return out
 
     __call__ = forward
+
+    def classify(self, x):
+        """Forward pass plus the per-video reduction on the GPU.
+
+        Returns ``(logits, total, cls)``: fp32 (B, num_classes), fp32 (num_classes,) = sum over
+        the clips, int32 scalar = arg-max of the sum -- engine-owned device tensors, asynchronous
+        on the current stream (what R2P1DAggregator computes on the host, model.py:254,259).
+        """
+        if self.end_index != 5:
+            raise ValueError('classify() needs a range that ends at layer 5')
+        x, fmt, batch = self._check_input(x)
+        if batch < 1:
+            raise ValueError('classify() needs at least one clip')
+        if not hasattr(self, '_sum'):
+            self._sum = torch.empty(self.num_classes, dtype=torch.float32, device=self.device)
+            self._cls = torch.empty((), dtype=torch.int32, device=self.device)
+        out = self._out[:batch]
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self.lib.rnb_r2p1d_classify(
+            self._handle, ctypes.c_void_p(x.data_ptr()), fmt, batch,
+            ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(self._sum.data_ptr()),
+            ctypes.c_void_p(self._cls.data_ptr()), ctypes.c_void_p(stream)))
+        return out, self._sum, self._cls

@@ -91,6 +91,39 @@ def logits_sum_argmax(logits, sum_out=None, cls_out=None):
     return sum_out, cls_out
 
 
+def pool_fc_classify(x, weight, bias, scratch=None, want_logits=True):
+    """Classifier tail in one launch: mean over positions, Linear, sum over clips, arg-max.
+
+    ``x``: bf16 (B, S, C) channels-last activations of the last stage; ``weight`` fp32 (classes, C);
+    ``bias`` fp32 (classes).  Returns ``(logits or None, total, cls)`` device tensors.  ``scratch`` is
+    a uint8 CUDA tensor of at least ``pool_fc_classify_scratch_bytes(B, classes)`` bytes (allocated
+    here when omitted).
+    """
+    lib = _lib.load()
+    if x.dtype != torch.bfloat16 or x.dim() != 3 or not x.is_cuda:
+        raise ValueError('x must be a CUDA bf16 (B, S, C) tensor')
+    x = x.contiguous()
+    weight = weight.contiguous()
+    bias = bias.contiguous()
+    batch, positions, channels = x.shape
+    classes = weight.shape[0]
+    need = int(lib.rnb_pool_fc_classify_scratch_bytes(batch, classes))
+    if scratch is None:
+        scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+    logits = torch.empty((batch, classes), dtype=torch.float32, device=x.device) \
+        if want_logits else None
+    total = torch.empty(classes, dtype=torch.float32, device=x.device)
+    cls = torch.empty((), dtype=torch.int32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.rnb_pool_fc_classify(
+            ctypes.c_void_p(x.data_ptr()), batch, positions, channels,
+            ctypes.c_void_p(weight.data_ptr()), ctypes.c_void_p(bias.data_ptr()), classes,
+            ctypes.c_void_p(logits.data_ptr()) if logits is not None else None,
+            ctypes.c_void_p(total.data_ptr()), ctypes.c_void_p(cls.data_ptr()),
+            ctypes.c_void_p(scratch.data_ptr()), scratch.numel(), _stream(x.device)))
+    return logits, total, cls
+
+
 def peer_copy(dst, src):
     """``dst.copy_(src)`` for same-shape contiguous CUDA tensors, possibly on different GPUs.
 

@@ -208,6 +208,47 @@ class R2P1DSingleStep(RunnerModel):
         return ((MAX_CLIPS, NUM_CLASSES),)
 
 
+class R2P1DVideoClassifier(RunnerModel):
+    """Loader, whole network and aggregation in one final step; emits the video's class id.
+
+    The per-clip logits never leave the GPU: the classifier kernel also sums over the clips and
+    takes the arg-max (what R2P1DAggregator does on the host).  The class id lands in a pinned host
+    tensor that is valid once the runner has synchronised its stream (runner.py:127-128); it is
+    returned as the non-tensor output.
+    """
+
+    def __init__(self, device, num_classes=NUM_CLASSES, layer_sizes=[2, 2, 2, 2], block_type=None,
+                 num_clips_population=[1, 15], num_clips_weights=[10, 1], dtype='bf16',
+                 checkpoint=None, state_dict=None, seed=0, max_batch=64, warmup=3):
+        super(R2P1DVideoClassifier, self).__init__(device)
+        from .engine import R2P1DEngine
+        self.device = torch.device(device)
+        full_sizes = [2] + list(layer_sizes)
+        sd = _resolve_state_dict(1, 5, num_classes, full_sizes, checkpoint, state_dict, seed)
+        self.model = R2P1DEngine(device, sd, 1, 5, num_classes, full_sizes, dtype=dtype,
+                                 max_batch=max(max_batch, MAX_CLIPS))
+        self.clips = _SyntheticClips(self.device, num_clips_population, num_clips_weights, seed)
+        self.cls_host = torch.empty((), dtype=torch.int32).pin_memory()
+        stream = torch.cuda.current_stream()
+        for _ in range(warmup):
+            self.model.classify(self.clips.pool)
+            stream.synchronize()
+
+    def __call__(self, tensors, non_tensors, time_card):
+        frames = self.clips.next()
+        time_card.num_clips = frames.shape[0]
+        _, _, cls = self.model.classify(frames)
+        self.cls_host.copy_(cls, non_blocking=True)
+        return None, self.cls_host, time_card
+
+    def input_shape(self):
+        return None
+
+    @staticmethod
+    def output_shape():
+        return None
+
+
 class R2P1DAggregator(RunnerModel):
     """Sums per-clip logits of a video (over its segments) and picks the class."""
 

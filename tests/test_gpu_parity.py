@@ -188,6 +188,60 @@ def test_logits_sum_argmax(lib):
     assert int(ops.logits_sum_argmax(tie.to(DEV))[1].item()) == 7  # numpy's lowest-index rule
 
 
+def test_pool_fc_classify_standalone(lib):
+    """pool -> view -> linear (network.py:35,41,56,60) -> sum over clips -> argmax (model.py:254,259)."""
+    from rnb_b200 import ops
+    g = torch.Generator().manual_seed(12)
+    lin = torch.nn.Linear(512, 400)
+    for batch in (1, 5, 15, 64):
+        x = torch.randn(batch, 49, 512, generator=g).relu().to(torch.bfloat16)
+        want = torch.nn.functional.linear(x.float().mean(dim=1), lin.weight, lin.bias).detach()
+        logits, total, cls = ops.pool_fc_classify(x.to(DEV), lin.weight.detach().to(DEV),
+                                                  lin.bias.detach().to(DEV))
+        assert float(rel_err_per_clip(logits.cpu(), want).max()) <= 1e-5
+        want_sum = want.numpy().sum(axis=0)
+        np.testing.assert_allclose(total.cpu().numpy(), want_sum, rtol=1e-5, atol=1e-5)
+        assert int(cls.item()) == int(total.cpu().numpy().argmax())
+        assert int(cls.item()) == int(want_sum.argmax())
+    # the caller's scratch may hold anything on entry, and is reusable back to back
+    need = int(lib.rnb_pool_fc_classify_scratch_bytes(15, 400))
+    scratch = torch.full((need,), 0xff, dtype=torch.uint8, device=DEV)
+    x = torch.randn(15, 49, 512, generator=g).to(torch.bfloat16).to(DEV)
+    a = ops.pool_fc_classify(x, lin.weight.detach().to(DEV), lin.bias.detach().to(DEV), scratch)
+    b = ops.pool_fc_classify(x, lin.weight.detach().to(DEV), lin.bias.detach().to(DEV), scratch)
+    assert torch.equal(a[1], b[1]) and int(a[2]) == int(b[2])
+    with pytest.raises(Exception):
+        ops.pool_fc_classify(x, lin.weight.detach().to(DEV), lin.bias.detach().to(DEV), scratch[:512])
+
+
+@pytest.mark.parametrize('dtype', ['bf16', 'fp32'])
+def test_engine_classify_matches_oracle_aggregator(engines, models, dtype):
+    clips = R.synthetic_clips(15, seed=55)
+    want = R.forward_u8(models[True], clips)
+    eng = engines(dtype, True)
+    logits, total, cls = eng.classify(clips.to(DEV))
+    check_logits(logits.cpu(), want, dtype)
+    np.testing.assert_allclose(total.cpu().numpy(), logits.cpu().numpy().sum(axis=0), rtol=1e-5,
+                               atol=1e-4)
+    assert int(cls.item()) == R.video_class(want)
+    # and identical logits to the plain forward
+    assert torch.equal(logits.clone(), eng(clips.to(DEV)))
+
+
+def test_video_classifier_step(lib, models):
+    from rnb_b200 import steps
+    from rnb_b200.timecard import TimeCard
+    dev = torch.device(DEV)
+    step = steps.R2P1DVideoClassifier(dev, state_dict=models[True].state_dict(), seed=3)
+    assert steps.R2P1DVideoClassifier.output_shape() is None
+    for vid in range(3):
+        tensors, cls_host, tc = step(None, 'v%d.mp4' % vid, TimeCard(vid))
+        torch.cuda.current_stream().synchronize()
+        n = tc.num_clips
+        want = R.forward_u8(models[True], step.clips.pool[:n].cpu())
+        assert tensors is None and int(cls_host) == R.video_class(want)
+
+
 def test_peer_copy_same_device(lib):
     from rnb_b200 import handoff
     src = torch.randn(5, 400, device=DEV)
