@@ -184,14 +184,6 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
       const size_t off = ((((size_t)tc.b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad;
       __nv_bfloat16* out_row = p.y + off;
       const __nv_bfloat16* res_row = kRes ? p.residual + off : nullptr;
-      // the residual does not depend on the accumulator: fetch the first chunk's 32 bytes before
-      // waiting for the MMA, and chunk i+1's while chunk i is converted
-      uint32_t rnext[8];
-      if (kRes) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) rnext[j] = 0u;
-        if (valid && half < nchunk) ptx::ld_global_nc_v8(res_row + half * 16, rnext);
-      }
       const long long tf0 = clock64();
       ptx::mbar_wait(tmem_full_bar + 8 * acc, acc_phase);
       wait_f += clock64() - tf0;
@@ -211,11 +203,8 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
         uint32_t rwd[8];
         if (kRes) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            rwd[j] = rnext[j];
-            rnext[j] = 0u;
-          }
-          if (valid && cchunk + 2 < nchunk) ptx::ld_global_nc_v8(res_row + col + 32, rnext);
+          for (int j = 0; j < 8; ++j) rwd[j] = 0u;
+          if (valid) ptx::ld_global_nc_v8(res_row + col, rwd);
         }
         ptx::tmem_ld_wait();
         uint32_t o[8];
