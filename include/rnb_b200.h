@@ -126,6 +126,35 @@ int rnb_pool_fc_classify(const void* x, int batch, int positions, int channels, 
                          const float* bias, int classes, float* logits, float* sum, int* cls,
                          void* scratch, size_t scratch_bytes, void* stream);
 
+/* rnb_pool_fc_classify for callers that cannot allocate device memory.  (No counterpart in the
+ * reference.)
+ *
+ * Who needs it: code that runs where cudaMalloc is off limits -- a serving process whose device
+ * memory was carved up once at start-up and then locked, a latency-critical loop that may not take
+ * the allocator's lock or sit through cudaMalloc's implicit device synchronisation, or a host
+ * application that only lends this library raw pointers and owns every allocation itself.  Such a
+ * caller has nowhere to get the scratch buffer rnb_pool_fc_classify asks for, so this variant
+ * brings its own: a fixed array compiled into the library, 256 bytes +
+ * RNB_STATIC_CLASSIFY_MAX_BATCH x RNB_STATIC_CLASSIFY_MAX_CLASSES floats (about 256 KiB) per GPU
+ * that loads the library, held until the process exits.  Same arguments and results as
+ * rnb_pool_fc_classify minus the scratch pair; x, w, bias and the outputs are still the caller's.
+ *
+ *  - Calls no cudaMalloc / cudaFree or any other allocating routine, on any call.
+ *  - batch > RNB_STATIC_CLASSIFY_MAX_BATCH or classes > RNB_STATIC_CLASSIFY_MAX_CLASSES is refused
+ *    with RNB_EINVAL and a message that names the limits.
+ *  - The first call on each device looks up the array's device address (with that device current)
+ *    and remembers it; make that first call before you start capturing a stream.
+ *  - All calls on one GPU share the one array.  Each call re-zeroes the part that must start at zero
+ *    (the arrival counter), so stale contents from the previous call are harmless, but two calls
+ *    that can overlap on the GPU (different streams, or different threads/processes' streams on the
+ *    same device within one process) race on it: serialise them, or use rnb_pool_fc_classify with
+ *    one scratch buffer per stream. */
+#define RNB_STATIC_CLASSIFY_MAX_BATCH 64
+#define RNB_STATIC_CLASSIFY_MAX_CLASSES 1024
+int rnb_pool_fc_classify_static(const void* x, int batch, int positions, int channels,
+                                const float* w, const float* bias, int classes, float* logits,
+                                float* sum, int* cls, void* stream);
+
 /* Concatenate k row-blocks (rows[i] rows of row_bytes bytes each, device pointers in the HOST
  * array srcs) into dst.  Replaces torch.cat(self.stacked_tensors, dim=0) at batcher.py:28. */
 int rnb_batch_gather(const void* const* srcs, const int* rows, int k, void* dst, size_t row_bytes,

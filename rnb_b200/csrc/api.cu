@@ -6,6 +6,10 @@
 #include "kernels.cuh"
 #include "model.cuh"
 
+static_assert(RNB_STATIC_CLASSIFY_MAX_BATCH == rnb::kStaticClassifyMaxBatch &&
+                  RNB_STATIC_CLASSIFY_MAX_CLASSES == rnb::kStaticClassifyMaxClasses,
+              "include/rnb_b200.h and kernels.cuh disagree on the built-in scratch size");
+
 namespace {
 
 thread_local std::string g_last_error;
@@ -136,6 +140,28 @@ int rnb_pool_fc_classify(const void* x, int batch, int positions, int channels, 
       static_cast<const __nv_bfloat16*>(x), batch, positions, channels, w, bias, classes, logits, sum,
       cls, scratch, static_cast<cudaStream_t>(stream));
   if (e != cudaSuccess) return cuda_fail(e, "rnb_pool_fc_classify");
+  return RNB_OK;
+}
+
+int rnb_pool_fc_classify_static(const void* x, int batch, int positions, int channels,
+                                const float* w, const float* bias, int classes, float* logits,
+                                float* sum, int* cls, void* stream) {
+  if (batch < 0 || positions < 1 || classes < 1 || channels < 8 || channels % 8 != 0)
+    return fail(RNB_EINVAL,
+                "rnb_pool_fc_classify_static: bad shape (channels must be a multiple of 8)");
+  if (batch > RNB_STATIC_CLASSIFY_MAX_BATCH || classes > RNB_STATIC_CLASSIFY_MAX_CLASSES)
+    return fail(RNB_EINVAL,
+                "rnb_pool_fc_classify_static: batch " + std::to_string(batch) + " x classes " +
+                    std::to_string(classes) + " exceeds the built-in scratch (at most " +
+                    std::to_string(RNB_STATIC_CLASSIFY_MAX_BATCH) + " clips x " +
+                    std::to_string(RNB_STATIC_CLASSIFY_MAX_CLASSES) +
+                    " classes); use rnb_pool_fc_classify with your own scratch buffer");
+  if (batch == 0) return RNB_OK;
+  if (!x || !w || !bias) return fail(RNB_EINVAL, "null pointer");
+  cudaError_t e = rnb::launch_pool_fc_classify_bf16_static(
+      static_cast<const __nv_bfloat16*>(x), batch, positions, channels, w, bias, classes, logits, sum,
+      cls, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return cuda_fail(e, "rnb_pool_fc_classify_static");
   return RNB_OK;
 }
 

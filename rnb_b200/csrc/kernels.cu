@@ -532,6 +532,42 @@ cudaError_t launch_pool_fc_classify_bf16(const __nv_bfloat16* x, int B, int S, i
   return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------ static scratch
+// Scratch of the no-allocation classifier entry point.  In HOST code this name is only a handle for
+// the runtime, not a device address: passing it to a kernel would fault (or silently touch host
+// memory on systems where the GPU can reach it).  The device address comes from
+// cudaGetSymbolAddress, per device, below.
+static __device__ __align__(256) unsigned char g_static_classify_scratch[kStaticClassifyScratchBytes];
+
+cudaError_t static_classify_scratch(void** ptr) {
+  constexpr int kMaxDevices = 64;
+  static void* resolved[kMaxDevices] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+  if (resolved[dev] == nullptr) {
+    // set-up, once per device, with that device current: every GPU has its own copy of the array
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_classify_scratch);
+    if (e != cudaSuccess) return e;
+    resolved[dev] = p;
+  }
+  *ptr = resolved[dev];
+  return cudaSuccess;
+}
+
+cudaError_t launch_pool_fc_classify_bf16_static(const __nv_bfloat16* x, int B, int S, int C,
+                                                const float* w, const float* bias, int num_classes,
+                                                float* logits, float* sum, int* cls, cudaStream_t s) {
+  void* scratch = nullptr;
+  cudaError_t e = static_classify_scratch(&scratch);
+  if (e != cudaSuccess) return e;
+  // same launcher as the caller-scratch entry point; it zeroes the arrival counter first, so
+  // whatever the previous call left in the shared array does not matter
+  return launch_pool_fc_classify_bf16(x, B, S, C, w, bias, num_classes, logits, sum, cls, scratch, s);
+}
+
 cudaError_t launch_batch_gather(const void* const* srcs, const int* rows, int k, void* dst,
                                 size_t row_bytes, cudaStream_t s) {
   if (k < 0 || k > kMaxGatherSrcs) return cudaErrorInvalidValue;

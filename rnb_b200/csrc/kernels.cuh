@@ -69,6 +69,19 @@ cudaError_t launch_pool_fc_classify_bf16(const __nv_bfloat16* x, int B, int S, i
                                          const float* bias, int num_classes, float* logits,
                                          float* sum, int* cls, void* scratch, cudaStream_t s);
 
+// Variant for callers that cannot allocate device memory: the scratch lives in a file-scope
+// __device__ array inside kernels.cu (one copy per GPU that loads the library, kept until exit).
+constexpr int kStaticClassifyMaxBatch = 64;
+constexpr int kStaticClassifyMaxClasses = 1024;
+constexpr size_t kStaticClassifyScratchBytes =
+    256 + (size_t)kStaticClassifyMaxBatch * kStaticClassifyMaxClasses * sizeof(float);
+// Resolves (once per device, for the CURRENT device) the device address of that array; returns
+// cudaSuccess and the pointer, or the error cudaGetSymbolAddress / cudaGetDevice reported.
+cudaError_t static_classify_scratch(void** ptr);
+cudaError_t launch_pool_fc_classify_bf16_static(const __nv_bfloat16* x, int B, int S, int C,
+                                                const float* w, const float* bias, int num_classes,
+                                                float* logits, float* sum, int* cls, cudaStream_t s);
+
 // ---- batching / aggregation ----------------------------------------------------------------------
 constexpr int kMaxGatherSrcs = 64;
 cudaError_t launch_batch_gather(const void* const* srcs, const int* rows, int k, void* dst,
