@@ -8,9 +8,9 @@
 //               box of the packed weights, into a multi-stage shared-memory ring.
 //   warp 1      allocates TMEM and issues tcgen05.mma (M=128, N<=256, K=16 per instruction) into one
 //               of two accumulator buffers, so the epilogue of tile i overlaps the main loop of i+1.
-//   warps 2-5   epilogue: tcgen05.ld the accumulator (lane == output position), folded BatchNorm /
-//               bias (scale, shift), optional residual add and ReLU, bf16 pack into a swizzled
-//               staging tile, TMA store (clipped at the tensor edge).
+//   warps 2-9   epilogue: tcgen05.ld the accumulator (lane == output position), folded BatchNorm /
+//               bias (shift; the scale lives in the weights), optional residual add and ReLU, bf16
+//               pack, one 32-byte global store per 16 channels (rows outside the tensor masked).
 #include <stdio.h>
 
 #include "conv_tc.cuh"
@@ -59,8 +59,7 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   const uint32_t a_bytes = kTileM * p.bk * 2;
   const uint32_t b_bytes = p.block_n * p.bk * 2;
   const uint32_t stage_bytes = a_bytes + b_bytes;
-  const uint32_t staging = smem_base + p.num_stages * stage_bytes;
-  const uint32_t bars = staging + 2 * kStagingBytes;
+  const uint32_t bars = smem_base + p.num_stages * stage_bytes;
   // barrier layout (8 bytes each): full[S], empty[S], tmem_full[2], tmem_empty[2], then tmem ptr
   const uint32_t full_bar = bars;
   const uint32_t empty_bar = bars + 8 * p.num_stages;
@@ -74,7 +73,6 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.a_map[0]);
     ptx::prefetch_tmap(&p.b_map);
-    ptx::prefetch_tmap(&p.d_map);
     for (int s = 0; s < p.num_stages; ++s) {
       ptx::mbar_init(full_bar + 8 * s, 1);
       ptx::mbar_init(empty_bar + 8 * s, 1);
@@ -162,114 +160,79 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
     }
   } else {
     // ------------------------------------------------------------------ epilogue (256 threads)
-    // Two warps share each TMEM lane quarter and take alternate 16-column chunks.
+    // Two warps share each TMEM lane quarter and take alternate 16-column chunks.  Every thread
+    // owns one output position (= TMEM lane) and writes its 16 channels as one 32-byte store; no
+    // staging tile, so all shared memory goes to the operand ring.
     const int ew = warp - 2;          // 0..7
     const int q = warp & 3;           // TMEM lane quarter this warp may read
-    const int half = ew >> 2;         // which chunks of a sub-tile this warp converts
+    const int half = ew >> 2;         // which chunks this warp converts
     const int row = q * 32 + lane;    // output position inside the tile
     const int et = threadIdx.x - 64;  // 0..255
-    const bool store_thread = (et == 0);
     const int lbb_shift = p.lbw + p.lbh + p.lbt;
     const int iw = row & ((1 << p.lbw) - 1);
     const int ih = (row >> p.lbw) & ((1 << p.lbh) - 1);
     const int it = (row >> (p.lbw + p.lbh)) & ((1 << p.lbt) - 1);
     const int ib = row >> lbb_shift;
-    const uint32_t rowaddr_off = row * 128;
-    const uint32_t rsw = row & 7;
     int local = 0;
-    uint32_t nstore = 0;
     int table_n0 = -1;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
       const TileCoord tc = decode_tile(p, tile);
       const uint32_t acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
-      const __nv_bfloat16* res_row = nullptr;
-      if (kRes) {
-        const int w = tc.w0 + iw, h = tc.h0 + ih, t = tc.t0 + it, b = tc.b0 + ib;
-        if ((w < p.Wo) && (h < p.Ho) && (t < p.To) && (b < p.B))
-          res_row = p.residual + ((((size_t)b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad;
-      }
+      const int w = tc.w0 + iw, h = tc.h0 + ih, t = tc.t0 + it, b = tc.b0 + ib;
+      const bool valid = (w < p.Wo) && (h < p.Ho) && (t < p.To) && (b < p.B);
+      const size_t off = ((((size_t)b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad + tc.n0;
+      __nv_bfloat16* out_row = p.y + off;
+      const __nv_bfloat16* res_row = kRes ? p.residual + off : nullptr;
       if (tc.n0 != table_n0) {
-        // per-channel shift of this channel tile -> shared memory (visible after the first barrier
-        // below; the previous tile's readers are all past their last barrier)
+        // per-channel shift of this channel tile -> shared memory.  The barrier before the write
+        // keeps it behind the previous tile's readers, the one after publishes it.
+        ptx::named_bar_sync(1, kEpiThreads);
         if (et < tc.ncols) {
           const float v = __ldg(p.shift + tc.n0 + et);
           asm volatile("st.shared.f32 [%0], %1;\n" ::"r"(shift_tab + et * 4), "f"(v) : "memory");
         }
+        ptx::named_bar_sync(1, kEpiThreads);
         table_n0 = tc.n0;
       }
       ptx::mbar_wait(tmem_full_bar + 8 * acc, acc_phase);
       ptx::tc_fence_after();
       const uint32_t taddr_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kMaxBlockN;
-      const int nsub = (tc.ncols + 63) >> 6;
-      for (int sub = 0; sub < nsub; ++sub) {
-        const int nchunk = min(64, tc.ncols - sub * 64) >> 4;  // 16-column chunks in this sub-tile
-        const uint32_t buf = staging + (nstore & 1) * kStagingBytes;
-        // the staging buffer used two stores ago must have been read by its TMA store
-        if (store_thread) ptx::tma_store_wait_read<1>();
-        ptx::named_bar_sync(1, kEpiThreads);
-        for (int cchunk = half; cchunk < nchunk; cchunk += 2) {
-          uint32_t v[16];
-          const int col = sub * 64 + cchunk * 16;
-          ptx::tmem_ld16(taddr_row + col, v);
-          uint64_t sh2[8];
+      const int nchunk = tc.ncols >> 4;
+      for (int cchunk = half; cchunk < nchunk; cchunk += 2) {
+        uint32_t v[16];
+        const int col = cchunk * 16;
+        ptx::tmem_ld16(taddr_row + col, v);
+        uint64_t sh2[8];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];\n"
-                         : "=l"(sh2[2 * j]), "=l"(sh2[2 * j + 1])
-                         : "r"(shift_tab + (col + 4 * j) * 4));
-          }
-          uint64_t r2[8];
-          if (kRes) {
-            uint32_t rw[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) rw[j] = 0u;
-            if (res_row != nullptr) {
-              const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(res_row + tc.n0 + col));
-              const uint4 r1 = __ldg(reinterpret_cast<const uint4*>(res_row + tc.n0 + col) + 1);
-              rw[0] = r0.x; rw[1] = r0.y; rw[2] = r0.z; rw[3] = r0.w;
-              rw[4] = r1.x; rw[5] = r1.y; rw[6] = r1.z; rw[7] = r1.w;
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              r2[j] = ptx::pack_f32x2(__uint_as_float(rw[j] << 16),
-                                      __uint_as_float(rw[j] & 0xffff0000u));
-          }
-          ptx::tmem_ld_wait();
-          uint32_t o[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            uint64_t x = ptx::add_f32x2(
-                ptx::pack_f32x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), sh2[j]);
-            if (kRes) x = ptx::add_f32x2(x, r2[j]);
-            o[j] = ptx::cvt_bf16x2<kRelu>(x);
-          }
-          // two 16-byte chunks of this row; 128-byte swizzle: chunk index XOR (row mod 8)
-          const uint32_t rowaddr = buf + rowaddr_off;
-          const uint32_t a0 = rowaddr + (((cchunk * 2) ^ rsw) << 4);
-          const uint32_t a1 = rowaddr + (((cchunk * 2 + 1) ^ rsw) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(a0), "r"(o[0]), "r"(o[1]),
-                       "r"(o[2]), "r"(o[3])
-                       : "memory");
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(a1), "r"(o[4]), "r"(o[5]),
-                       "r"(o[6]), "r"(o[7])
-                       : "memory");
+        for (int j = 0; j < 4; ++j) {
+          asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];\n"
+                       : "=l"(sh2[2 * j]), "=l"(sh2[2 * j + 1])
+                       : "r"(shift_tab + (col + 4 * j) * 4));
         }
-        if (sub == nsub - 1) {
-          // every TMEM read of this accumulator buffer has completed: hand it back to the MMA warp
-          ptx::tc_fence_before();
-          ptx::mbar_arrive(tmem_empty_bar + 8 * acc);
+        uint32_t rwd[8];
+        if (kRes) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) rwd[j] = 0u;
+          if (valid) ptx::ld_global_nc_v8(res_row + col, rwd);
         }
-        ptx::fence_proxy_async_smem();
-        ptx::named_bar_sync(1, kEpiThreads);
-        if (store_thread) {
-          ptx::tma_store_5d(&p.d_map, buf, tc.n0 + sub * 64, tc.w0, tc.h0, tc.t0, tc.b0);
-          ptx::tma_store_commit();
+        ptx::tmem_ld_wait();
+        uint32_t o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          uint64_t x = ptx::add_f32x2(
+              ptx::pack_f32x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), sh2[j]);
+          if (kRes)
+            x = ptx::add_f32x2(x, ptx::pack_f32x2(__uint_as_float(rwd[j] << 16),
+                                                  __uint_as_float(rwd[j] & 0xffff0000u)));
+          o[j] = ptx::cvt_bf16x2<kRelu>(x);
         }
-        ++nstore;
+        if (valid) ptx::st_global_v8(out_row + col, o);
       }
+      // every TMEM read of this accumulator buffer has completed: hand it back to the MMA warp
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(tmem_empty_bar + 8 * acc);
     }
-    if (store_thread) ptx::tma_store_wait_all<0>();
   }
 
   ptx::tc_fence_before();

@@ -13,7 +13,6 @@ constexpr int kMaxBlockN = 256;      // accumulator columns per tile
 constexpr int kTmemCols = 512;       // two accumulator buffers
 constexpr int kConvThreads = 320;    // warp0 TMA, warp1 MMA, warps2-9 epilogue
 constexpr int kEpiThreads = 256;
-constexpr int kStagingBytes = 16384; // one 128 x 64 bf16 output sub-tile
 constexpr int kSmemLimit = 232448;   // 227 KB
 
 // One output tile is a box of 128 output positions (bw x bh x bt x bb, powers of two) by up to
@@ -22,7 +21,7 @@ constexpr int kSmemLimit = 232448;   // 227 KB
 struct ConvTcParams {
   alignas(64) CUtensorMap a_map[4];  // activation views, dims (C, W, H, T, B), bf16
   alignas(64) CUtensorMap b_map;     // packed weights, dims (K_total, N_rows), bf16, K-major
-  alignas(64) CUtensorMap d_map;     // output, dims (C, W, H, T, B), bf16
+  __nv_bfloat16* y;                  // output (B, To, Ho, Wo, cout_pad), written by plain stores
   const float* shift;                // per output channel (BatchNorm scale is folded into the weights)
   const __nv_bfloat16* residual;     // same layout as the output, or nullptr
   int num_taps;
@@ -48,8 +47,8 @@ inline int conv_tc_stage_bytes(int bk, int block_n) { return (kTileM + block_n) 
 
 // Dynamic shared memory the kernel needs for a given configuration.
 inline int conv_tc_smem_bytes(int bk, int block_n, int stages) {
-  return 1024 /*alignment slack*/ + stages * conv_tc_stage_bytes(bk, block_n) + 2 * kStagingBytes +
-         256 /*barriers*/ + kMaxBlockN * 4 /*shift table*/;
+  return 1024 /*alignment slack*/ + stages * conv_tc_stage_bytes(bk, block_n) + 256 /*barriers*/ +
+         kMaxBlockN * 4 /*shift table*/;
 }
 
 cudaError_t launch_conv_tc(const ConvTcParams& p, int num_sms, cudaStream_t stream);

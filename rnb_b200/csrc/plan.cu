@@ -204,7 +204,7 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   }
   const int stage_bytes = conv_tc_stage_bytes(p.bk, p.block_n);
   int stages = (kSmemLimit - conv_tc_smem_bytes(p.bk, p.block_n, 0)) / stage_bytes;
-  if (stages > 8) stages = 8;
+  if (stages > 10) stages = 10;
   if (stages < 2) {
     if (err) *err = "conv_tc: pipeline does not fit in shared memory";
     return false;
@@ -280,15 +280,7 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
     const uint32_t box[2] = {(uint32_t)p.bk, (uint32_t)p.block_n};
     if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, swz, err)) return false;
   }
-  {
-    const uint64_t dims[5] = {(uint64_t)np, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)g.To,
-                              (uint64_t)B};
-    const uint64_t strides[4] = {(uint64_t)np * 2, (uint64_t)g.Wo * np * 2,
-                                 (uint64_t)g.Ho * g.Wo * np * 2,
-                                 (uint64_t)g.To * g.Ho * g.Wo * np * 2};
-    const uint32_t box[5] = {64u, (uint32_t)bw, (uint32_t)bh, (uint32_t)bt, (uint32_t)bb};
-    if (!encode_bf16(&p.d_map, y, 5, dims, strides, box, 128, err)) return false;
-  }
+  p.y = y;
   return true;
 }
 
