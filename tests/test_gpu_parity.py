@@ -339,3 +339,17 @@ def test_batcher_copies_instead_of_aliasing(lib):
     # pass-through when batch <= 1 (batcher.py:18-19)
     t = (placeholder[:2],)
     assert steps.Batcher(dev, batch=1)(t, 'x', 'tc') == (t, 'x', 'tc')
+
+
+def test_peer_copy_across_gpus(lib):
+    """Segment hand-off between two GPUs (runner.py:112-113,170) over NVLink peer copy."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs')
+    from rnb_b200 import handoff
+    src = torch.randn(15, 400, device='cuda:0')
+    shared = torch.zeros(15, 400, device='cuda:1')
+    n = handoff.publish(shared, src[:5].contiguous())          # producer on GPU 0 pushes
+    placeholder = torch.zeros(15, 400, device='cuda:0')
+    got = handoff.fetch(placeholder, shared, n)                # consumer pulls it back
+    assert n == 5 and torch.equal(got, src[:5])
+    assert torch.equal(shared[:5].cpu(), src[:5].cpu())
