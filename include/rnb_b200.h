@@ -97,11 +97,12 @@ int rnb_r2p1d_num_launches(void* handle);
  * capacity of ms and must be >= rnb_r2p1d_num_launches().  Synchronises `stream` before returning.
  * rnb_r2p1d_op_info() describes convolution `op` (0-based): its state_dict prefix, algorithmic
  * FLOPs per clip, and the bytes per clip it must move at least once (input + output + residual
- * activations in the handle's dtype; weights are per batch and reported separately). */
+ * activations in the handle's dtype; weights are per batch and reported separately), and which
+ * kernel runs it: 0 = fp32 direct convolution, 1 = conv_tc_kernel, 2 = conv_patch_kernel. */
 int rnb_r2p1d_profile(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
                       void* stream, float* ms, int cap);
 int rnb_r2p1d_op_info(void* handle, int op, char* name, int name_cap, double* flops_per_clip,
-                      double* act_bytes_per_clip, double* weight_bytes);
+                      double* act_bytes_per_clip, double* weight_bytes, int* kernel_kind);
 
 void rnb_r2p1d_destroy(void* handle);
 

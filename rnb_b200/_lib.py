@@ -52,7 +52,7 @@ PROTOTYPES = {
     'rnb_r2p1d_op_info': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p,
                                          ctypes.c_int, ctypes.POINTER(ctypes.c_double),
                                          ctypes.POINTER(ctypes.c_double),
-                                         ctypes.POINTER(ctypes.c_double)]),
+                                         ctypes.POINTER(ctypes.c_double), _c_int_p]),
     'rnb_r2p1d_io_shape': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _c_i64_p]),
     'rnb_r2p1d_flops': (ctypes.c_double, [ctypes.c_void_p, ctypes.c_int]),
     'rnb_r2p1d_num_launches': (ctypes.c_int, [ctypes.c_void_p]),

@@ -179,11 +179,11 @@ int rnb_r2p1d_profile(void* handle, const void* in, int in_fmt, int batch, void*
 }
 
 int rnb_r2p1d_op_info(void* handle, int op, char* name, int name_cap, double* flops_per_clip,
-                      double* act_bytes_per_clip, double* weight_bytes) {
+                      double* act_bytes_per_clip, double* weight_bytes, int* kernel_kind) {
   auto* m = static_cast<rnb::R2P1DModel*>(handle);
   if (!m || !m->finalized()) return fail(RNB_ESTATE, "handle not finalized");
   std::string n;
-  if (!m->op_info(op, &n, flops_per_clip, act_bytes_per_clip, weight_bytes))
+  if (!m->op_info(op, &n, flops_per_clip, act_bytes_per_clip, weight_bytes, kernel_kind))
     return fail(RNB_EINVAL, "op index out of range");
   if (name && name_cap > 0) {
     snprintf(name, (size_t)name_cap, "%s", n.c_str());

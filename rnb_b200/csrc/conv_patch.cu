@@ -91,16 +91,20 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
+  ptx::grid_dep_launch_dependents();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
   tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (warp-wide)
+    // the packed weights are constants of the model: fetch them while the previous kernel in the
+    // stream is still draining, and only then wait for its activations
     ptx::mbar_expect_tx_elect(w_full, n_wtiles * wtile_bytes);
     for (int tap = 0, i = 0; tap < p.num_taps; ++tap)
       for (int kb = 0; kb < p.nkb; ++kb, ++i)
         ptx::tma_load_2d_elect(wbuf + i * wtile_bytes, &p.b_map, w_full, tap * p.cin_pad + kb * 64, 0);
+    ptx::grid_dep_wait();
     int local = 0;
     long long wait_a = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
@@ -119,6 +123,8 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     if (p.dbg && lane == 0) p.dbg[blockIdx.x * 8 + 0] = wait_a;
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (warp-wide)
+    // (reads only shared memory and TMEM: ordered behind the producer's grid_dep_wait by the
+    // patch-full barrier)
     const uint32_t idesc = ptx::make_idesc_bf16_m128((uint32_t)p.n);
     const long long tm0 = clock64();
     ptx::mbar_wait(w_full, 0);
@@ -163,6 +169,7 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     }
   } else {
     // ------------------------------------------------------------------ epilogue (256 threads)
+    ptx::grid_dep_wait();  // residual reads and output stores must not pass the previous kernel
     const int ew = warp - 2;
     const int q = warp & 3;
     const int half = ew >> 2;
@@ -249,8 +256,17 @@ cudaError_t launch_patch_variant(const ConvPatchParams& p, int grid, int smem, c
     if (e != cudaSuccess) return e;
     configured[dev] = true;
   }
-  conv_patch_kernel<kRes, kRelu><<<grid, kConvThreads, smem, stream>>>(p);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kConvThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, conv_patch_kernel<kRes, kRelu>, p);
 }
 }  // namespace
 

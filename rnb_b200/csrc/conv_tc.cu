@@ -90,6 +90,10 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
+  // everything above touched only shared memory, TMEM and kernel parameters; from here on we read
+  // what the previous kernel in the stream wrote and overwrite what it may still be reading
+  ptx::grid_dep_launch_dependents();
+  ptx::grid_dep_wait();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
   tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
@@ -256,8 +260,17 @@ cudaError_t launch_variant(const ConvTcParams& p, int grid, int smem, cudaStream
     if (e != cudaSuccess) return e;
     configured[dev] = true;
   }
-  conv_tc_kernel<kRes, kRelu><<<grid, kConvThreads, smem, stream>>>(p);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kConvThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, conv_tc_kernel<kRes, kRelu>, p);
 }
 }  // namespace
 

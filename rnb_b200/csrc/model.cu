@@ -333,7 +333,7 @@ double R2P1DModel::flops(int batch) const {
 }
 
 bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
-                         double* act_bytes_per_clip, double* weight_bytes) const {
+                         double* act_bytes_per_clip, double* weight_bytes, int* kernel_kind) const {
   if (op < 0 || op >= (int)ops_.size()) return false;
   const ConvOp& o = ops_[op];
   const double es = (double)elem_size();
@@ -345,6 +345,8 @@ bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
           (double)o.g.To * o.g.Ho * o.g.Wo * o.g.cout * (o.res_slot >= 0 ? 2 : 1);
   }
   if (name) *name = o.name;
+  if (kernel_kind)
+    *kernel_kind = dtype_ != RNB_DTYPE_BF16 ? 0 : (conv_patch_applicable(o.g) ? 2 : 1);
   if (flops_per_clip) *flops_per_clip = o.g.flops(1);
   if (act_bytes_per_clip) *act_bytes_per_clip = act * es;
   if (weight_bytes)

@@ -47,7 +47,7 @@ class R2P1DModel {
   int profile(const void* in, int in_fmt, int batch, void* out, int out_fmt, cudaStream_t stream,
               float* ms, int cap, std::string* err);
   bool op_info(int op, std::string* name, double* flops_per_clip, double* act_bytes_per_clip,
-               double* weight_bytes) const;
+               double* weight_bytes, int* kernel_kind) const;
   void io_shape(int which, int64_t shape4[4]) const;
   double flops(int batch) const;
   int num_launches() const { return (int)ops_.size() + 2; }

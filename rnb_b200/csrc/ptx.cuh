@@ -69,6 +69,17 @@ __device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
   __syncwarp();
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// wait: block until the grid this one depends on has completed and its writes are visible;
+// launch_dependents: allow the next grid in the stream to begin launching (its CTAs become resident
+// as ours retire, so its prologue overlaps our tail).  Both are no-ops without the launch attribute.
+__device__ __forceinline__ void grid_dep_wait() {
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");
+}
+__device__ __forceinline__ void grid_dep_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+}
+
 // ---------------------------------------------------------------- fences / barriers
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");

@@ -176,14 +176,17 @@ class R2P1DEngine:
         return int(self.lib.rnb_r2p1d_num_launches(self._handle))
 
     def op_info(self):
-        """[(state_dict prefix, FLOPs per clip, activation bytes per clip, weight bytes)] per conv."""
+        """[(state_dict prefix, FLOPs per clip, activation bytes per clip, weight bytes, kernel)]
+        per convolution; kernel is 'conv_ref', 'conv_tc' or 'conv_patch'."""
         info = []
         for i in range(self.num_launches - 2):
             name = ctypes.create_string_buffer(256)
-            f, a, w = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+            f, a, w, k = ctypes.c_double(), ctypes.c_double(), ctypes.c_double(), ctypes.c_int()
             _lib.check(self.lib.rnb_r2p1d_op_info(self._handle, i, name, 256, ctypes.byref(f),
-                                                  ctypes.byref(a), ctypes.byref(w)))
-            info.append((name.value.decode(), f.value, a.value, w.value))
+                                                  ctypes.byref(a), ctypes.byref(w),
+                                                  ctypes.byref(k)))
+            info.append((name.value.decode(), f.value, a.value, w.value,
+                         ('conv_ref', 'conv_tc', 'conv_patch')[k.value]))
         return info
 
     def profile(self, x):
