@@ -24,10 +24,10 @@ struct TileCoord {
   int w0, h0, t0, b0, n0, ncols;
 };
 
-__device__ __forceinline__ TileCoord decode_tile(const ConvTcParams& p, int tile) {
+// position tile m (may be >= m_tiles for the padding CTAs of a cluster: its batch origin then
+// lies outside the tensor) and channel tile nt (ncols <= 0 when it lies beyond the last tile)
+__device__ __forceinline__ TileCoord decode_tile(const ConvTcParams& p, int m, int nt) {
   TileCoord c;
-  const int nt = tile % p.n_tiles;
-  int m = tile / p.n_tiles;
   const int iw = m % p.tiles_w;
   m /= p.tiles_w;
   const int ih = m % p.tiles_h;
@@ -44,6 +44,16 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvTcParams& p, int tile
   return c;
 }
 
+// work items of a cluster: groups of cm position tiles x cn channel tiles, channel group fastest
+struct ItemIter {
+  int n_groups, total, rm, rn, cm, cn;
+  __device__ __forceinline__ void tile(int item, int* m, int* nt) const {
+    const int ng = item % n_groups;
+    const int mg = item / n_groups;
+    *m = mg * cm + rm;
+    *nt = ng * cn + rn;
+  }
+};
 
 }  // namespace
 
@@ -68,14 +78,31 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   const uint32_t tmem_ptr_smem = tmem_empty_bar + 16;
   const uint32_t shift_tab = bars + 256;  // kMaxBlockN floats
 
-  const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b * p.n_tiles;
+  // ---- cluster geometry
+  const int csize = p.cm * p.cn;
+  const uint32_t crank = csize > 1 ? ptx::cluster_ctarank() : 0u;
+  ItemIter items;
+  items.cm = p.cm;
+  items.cn = p.cn;
+  items.rm = crank % p.cm;
+  items.rn = crank / p.cm;
+  items.n_groups = (p.n_tiles + p.cn - 1) / p.cn;
+  items.total = ((p.m_tiles + p.cm - 1) / p.cm) * items.n_groups;
+  const int first_item = blockIdx.x / csize;
+  const int item_step = gridDim.x / csize;
+  uint16_t a_mask = 0, b_mask = 0;  // CTAs that need my slice of A (same rm) / of B (same rn)
+  for (int j = 0; j < p.cn; ++j) a_mask |= (uint16_t)(1u << (items.rm + j * p.cm));
+  for (int i = 0; i < p.cm; ++i) b_mask |= (uint16_t)(1u << (i + items.rn * p.cm));
+  const uint16_t peers_mask = a_mask | b_mask;  // everyone that writes into my stages, me included
+  const uint32_t a_slice_bytes = a_bytes / p.cn;
+  const uint32_t b_slice_bytes = b_bytes / p.cm;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.a_map[0]);
     ptx::prefetch_tmap(&p.b_map);
     for (int s = 0; s < p.num_stages; ++s) {
       ptx::mbar_init(full_bar + 8 * s, 1);
-      ptx::mbar_init(empty_bar + 8 * s, 1);
+      ptx::mbar_init(empty_bar + 8 * s, p.cm + p.cn - 1);
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(tmem_full_bar + 8 * s, 1);
@@ -89,6 +116,9 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   }
   ptx::tc_fence_before();
   __syncthreads();
+  // peers multicast into my stages and arrive on my barriers: nobody may start before every CTA
+  // of the cluster has initialised its barriers
+  if (csize > 1) ptx::cluster_sync_all();
   ptx::tc_fence_after();
   // everything above touched only shared memory, TMEM and kernel parameters; from here on we read
   // what the previous kernel in the stream wrote and overwrite what it may still be reading
@@ -102,22 +132,41 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
     // ------------------------------------------------------------------ TMA producer (warp-wide,
     // one elected lane issues; see conv_patch.cu for why the roles are not run under lane == 0)
     uint32_t stage = 0, phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const TileCoord tc = decode_tile(p, tile);
+    // my slice of the activation box: offset along the split dimension, and where it lands
+    const int sl = items.rn * p.a_slice_step;
+    const int sl_w = p.a_slice_dim == 0 ? sl : 0, sl_h = p.a_slice_dim == 1 ? sl : 0;
+    const int sl_t = p.a_slice_dim == 2 ? sl : 0, sl_b = p.a_slice_dim == 3 ? sl : 0;
+    const uint32_t a_dst = items.rn * a_slice_bytes;
+    const uint32_t b_dst = a_bytes + items.rm * b_slice_bytes;
+    const int b_row = items.rm * (p.block_n / p.cm);
+    for (int item = first_item; item < items.total; item += item_step) {
+      int m, nt;
+      items.tile(item, &m, &nt);
+      const TileCoord tc = decode_tile(p, m, nt);
       for (int tap = 0; tap < p.num_taps; ++tap) {
         const void* amap = &p.a_map[p.tap_map[tap]];
-        const int cw = tc.w0 + p.tap_dw[tap];
-        const int ch = tc.h0 + p.tap_dh[tap];
-        const int ct = tc.t0 + p.tap_dt[tap];
+        const int cw = tc.w0 + p.tap_dw[tap] + sl_w;
+        const int ch = tc.h0 + p.tap_dh[tap] + sl_h;
+        const int ct = tc.t0 + p.tap_dt[tap] + sl_t;
+        const int cb = tc.b0 + sl_b;
         const int coff = p.tap_coff[tap];
         const int koff = p.tap_koff[tap];
         for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+          // free in EVERY CTA my slices go to (their MMA warps all arrive here)
           ptx::mbar_wait(empty_bar + 8 * stage, phase ^ 1);
           const uint32_t fb = full_bar + 8 * stage;
           const uint32_t sa = smem_base + stage * stage_bytes;
           ptx::mbar_expect_tx_elect(fb, stage_bytes);
-          ptx::tma_load_5d_elect(sa, amap, fb, coff + kb * p.bk, cw, ch, ct, tc.b0);
-          ptx::tma_load_2d_elect(sa + a_bytes, &p.b_map, fb, koff + kb * p.bk, tc.n0);
+          if (p.cn > 1)
+            ptx::tma_load_5d_mcast_elect(sa + a_dst, amap, fb, coff + kb * p.bk, cw, ch, ct, cb,
+                                         a_mask);
+          else
+            ptx::tma_load_5d_elect(sa, amap, fb, coff + kb * p.bk, cw, ch, ct, cb);
+          if (p.cm > 1)
+            ptx::tma_load_2d_mcast_elect(sa + b_dst, &p.b_map, fb, koff + kb * p.bk, tc.n0 + b_row,
+                                         b_mask);
+          else
+            ptx::tma_load_2d_elect(sa + a_bytes, &p.b_map, fb, koff + kb * p.bk, tc.n0);
           if (++stage == (uint32_t)p.num_stages) {
             stage = 0;
             phase ^= 1;
@@ -130,11 +179,14 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
     const uint32_t swz = p.bk * 2;  // bytes per operand row == swizzle span
     uint32_t stage = 0, phase = 0;
     int local = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
-      const TileCoord tc = decode_tile(p, tile);
+    for (int item = first_item; item < items.total; item += item_step, ++local) {
+      int m, nt;
+      items.tile(item, &m, &nt);
+      const TileCoord tc = decode_tile(p, m, nt);
+      const bool live = tc.ncols > 0;  // padding CTA of a cluster: keeps the barriers moving only
       const uint32_t acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
-      const uint32_t idesc = ptx::make_idesc_bf16_m128((uint32_t)tc.ncols);
+      const uint32_t idesc = ptx::make_idesc_bf16_m128((uint32_t)(live ? tc.ncols : 16));
       const uint32_t tmem_d = tmem_base + acc * kMaxBlockN;
       ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1);
       ptx::tc_fence_after();
@@ -148,12 +200,18 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
           const uint64_t bdesc = ptx::make_kmajor_desc(sa + a_bytes, swz);
           const int ksteps = min(p.bk, p.cin_pad - kb * p.bk) >> 4;
           // advancing 16 bf16 = 32 bytes along K inside the swizzle span: +2 in the address field
-          ptx::umma_bf16_elect(tmem_d, adesc, bdesc, idesc, accumulate);
-          if (ksteps > 1) ptx::umma_bf16_elect(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
-          if (ksteps > 2) ptx::umma_bf16_elect(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
-          if (ksteps > 3) ptx::umma_bf16_elect(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
+          if (live) {
+            ptx::umma_bf16_elect(tmem_d, adesc, bdesc, idesc, accumulate);
+            if (ksteps > 1) ptx::umma_bf16_elect(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
+            if (ksteps > 2) ptx::umma_bf16_elect(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
+            if (ksteps > 3) ptx::umma_bf16_elect(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
+          }
           accumulate = 1;
-          ptx::umma_commit_elect(empty_bar + 8 * stage);
+          // the stage may be refilled once its readers are done: tell every CTA that writes into it
+          if (csize > 1)
+            ptx::umma_commit_mcast_elect(empty_bar + 8 * stage, peers_mask);
+          else
+            ptx::umma_commit_elect(empty_bar + 8 * stage);
           if (++stage == (uint32_t)p.num_stages) {
             stage = 0;
             phase ^= 1;
@@ -179,8 +237,10 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
     const int ib = row >> lbb_shift;
     int local = 0;
     int table_n0 = -1;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
-      const TileCoord tc = decode_tile(p, tile);
+    for (int item = first_item; item < items.total; item += item_step, ++local) {
+      int m, nt;
+      items.tile(item, &m, &nt);
+      const TileCoord tc = decode_tile(p, m, nt);
       const uint32_t acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
       const int w = tc.w0 + iw, h = tc.h0 + ih, t = tc.t0 + it, b = tc.b0 + ib;
@@ -202,7 +262,7 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
       ptx::mbar_wait(tmem_full_bar + 8 * acc, acc_phase);
       ptx::tc_fence_after();
       const uint32_t taddr_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kMaxBlockN;
-      const int nchunk = tc.ncols >> 4;
+      const int nchunk = tc.ncols > 0 ? tc.ncols >> 4 : 0;
       for (int cchunk = half; cchunk < nchunk; cchunk += 2) {
         uint32_t v[16];
         const int col = cchunk * 16;
@@ -241,6 +301,8 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
 
   ptx::tc_fence_before();
   __syncthreads();
+  // a peer may still be multicasting its last arrivals into my barriers
+  if (csize > 1) ptx::cluster_sync_all();
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, kTmemCols);
@@ -249,7 +311,7 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
 
 namespace {
 template <bool kRes, bool kRelu>
-cudaError_t launch_variant(const ConvTcParams& p, int grid, int smem, cudaStream_t stream) {
+cudaError_t launch_variant(const ConvTcParams& p, int num_sms, int smem, cudaStream_t stream) {
   static bool configured[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -260,29 +322,49 @@ cudaError_t launch_variant(const ConvTcParams& p, int grid, int smem, cudaStream
     if (e != cudaSuccess) return e;
     configured[dev] = true;
   }
+  const int csize = p.cm * p.cn;
+  const int items = ((p.m_tiles + p.cm - 1) / p.cm) * ((p.n_tiles + p.cn - 1) / p.cn);
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  int max_clusters = num_sms / csize;
+  if (csize > 1) {
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = csize;
+    attr[1].val.clusterDim.y = 1;
+    attr[1].val.clusterDim.z = 1;
+    cfg.numAttrs = 2;
+    // how many clusters of this shape the device can hold at once (GPC boundaries strand SMs)
+    static int cached[64][5] = {};
+    if (dev >= 0 && dev < 64 && cached[dev][csize] == 0) {
+      cfg.gridDim = dim3(csize * (num_sms / csize));
+      int n = 0;
+      e = cudaOccupancyMaxActiveClusters(&n, conv_tc_kernel<kRes, kRelu>, &cfg);
+      if (e != cudaSuccess) return e;
+      cached[dev][csize] = n > 0 ? n : 1;
+    }
+    if (dev >= 0 && dev < 64 && cached[dev][csize] < max_clusters) max_clusters = cached[dev][csize];
+  }
+  const int clusters = items < max_clusters ? items : max_clusters;
+  cfg.gridDim = dim3(clusters * csize);
   return cudaLaunchKernelEx(&cfg, conv_tc_kernel<kRes, kRelu>, p);
 }
 }  // namespace
 
 cudaError_t launch_conv_tc(const ConvTcParams& p, int num_sms, cudaStream_t stream) {
   const int smem = conv_tc_smem_bytes(p.bk, p.block_n, p.num_stages);
-  const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b * p.n_tiles;
-  const int grid = total_tiles < num_sms ? total_tiles : num_sms;
+  if (p.cm < 1 || p.cn < 1 || p.cm * p.cn > 4) return cudaErrorInvalidValue;
   const bool res = p.residual != nullptr, relu = p.relu != 0;
-  if (res) return relu ? launch_variant<true, true>(p, grid, smem, stream)
-                       : launch_variant<true, false>(p, grid, smem, stream);
-  return relu ? launch_variant<false, true>(p, grid, smem, stream)
-              : launch_variant<false, false>(p, grid, smem, stream);
+  if (res) return relu ? launch_variant<true, true>(p, num_sms, smem, stream)
+                       : launch_variant<true, false>(p, num_sms, smem, stream);
+  return relu ? launch_variant<false, true>(p, num_sms, smem, stream)
+              : launch_variant<false, false>(p, num_sms, smem, stream);
 }
 
 }  // namespace rnb

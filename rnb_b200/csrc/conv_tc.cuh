@@ -35,6 +35,13 @@ struct ConvTcParams {
   int cout_pad;       // stored output channels (multiple of 16)
   int relu;
   int num_stages;
+  // thread-block cluster of cm x cn CTAs: the cm CTAs along M work on the same channel tile and
+  // each fetch 1/cm of the weight tile, multicast to all of them; the cn CTAs along N work on the
+  // same position tile and each fetch 1/cn of the activation tile (split along box dimension
+  // a_slice_dim: 0 = w, 1 = h, 2 = t, 3 = b).  cm = cn = 1: no cluster.
+  int cm, cn;
+  int m_tiles;
+  int a_slice_dim, a_slice_step;
   int8_t tap_map[kMaxTaps];
   int8_t tap_dw[kMaxTaps];
   int8_t tap_dh[kMaxTaps];

@@ -1,5 +1,7 @@
 #include "plan.cuh"
 
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -152,8 +154,9 @@ struct View {
 }  // namespace
 
 bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
-                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift, const __nv_bfloat16* residual, bool relu, int num_sms,
-                          ConvTcParams* out, std::string* err) {
+                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
+                          const __nv_bfloat16* residual, bool relu, int num_sms, ConvTcParams* out,
+                          std::string* err, int force_cm, int force_cn) {
   ConvTcParams& p = *out;
   memset(&p, 0, sizeof p);
   const int cp = g.cin_pad();
@@ -211,6 +214,47 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   }
   p.num_stages = stages;
 
+  // ---- thread-block cluster: share operand tiles between CTAs by TMA multicast where that cuts
+  // the L2 -> shared-memory traffic per tile (the bound of the conv3-5 layers)
+  p.m_tiles = m_tiles;
+  // the activation box is split along its slowest non-unit dimension so slices stay contiguous
+  const int ext[4] = {bw, bh, bt, bb};
+  int sdim = 0;
+  for (int d = 3; d >= 0; --d)
+    if (ext[d] > 1) {
+      sdim = d;
+      break;
+    }
+  int best_cm = 1, best_cn = 1;
+  {
+    if (force_cm <= 0)
+      if (const char* e = getenv("RNB_B200_CLUSTER")) sscanf(e, "%dx%d", &force_cm, &force_cn);
+    const double a_b = (double)kTileM * p.bk * 2;
+    const double b_b = (double)np / p.n_tiles * p.bk * 2;
+    double best_cost = -1;
+    static const int cand[6][2] = {{1, 1}, {2, 1}, {1, 2}, {2, 2}, {4, 1}, {1, 4}};
+    for (const auto& c : cand) {
+      const int cm = c[0], cn = c[1], cs = cm * cn;
+      if (force_cm > 0 && (cm != force_cm || cn != force_cn)) continue;
+      if (cn > 1 && ext[sdim] % cn != 0) continue;
+      if (cm > 1 && (p.block_n % (8 * cm) != 0)) continue;
+      // clusters of 4 cannot use every SM (GPC boundaries); measured ~33 of 37 on B200
+      const int max_clusters = cs == 4 ? (num_sms / 4) * 9 / 10 : num_sms / cs;
+      const int items = ceil_div(m_tiles, cm) * ceil_div(p.n_tiles, cn);
+      const int rounds = ceil_div(items, max_clusters > 0 ? max_clusters : 1);
+      const double cost = rounds * (a_b / cn + b_b / cm);
+      if (best_cost < 0 || cost < best_cost * 0.97) {  // prefer the smaller cluster on near-ties
+        best_cost = cost;
+        best_cm = cm;
+        best_cn = cn;
+      }
+    }
+  }
+  p.cm = best_cm;
+  p.cn = best_cn;
+  p.a_slice_dim = sdim;
+  p.a_slice_step = ext[sdim] / p.cn;
+
   // ---- taps and activation views
   std::vector<View> views;
   auto view_index = [&](int pw, int ph, int pt) {
@@ -228,10 +272,23 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
       *shift = (off - *par) / 2;
     }
   };
-  int ntap = 0;
+  // a tap whose input coordinate lies in the zero padding for EVERY output position contributes
+  // nothing (conv5's temporal convolutions run on T = 1: only the centre tap is live)
+  auto tap_live = [](int d, int pad, int stride, int in_ext, int out_ext) {
+    for (int o = 0; o < out_ext; ++o) {
+      const int i = o * stride + d - pad;
+      if (i >= 0 && i < in_ext) return true;
+    }
+    return false;
+  };
+  int ntap = 0, tap_index = -1;
   for (int dt = 0; dt < g.kt; ++dt)
     for (int dh = 0; dh < g.kh; ++dh)
       for (int dw = 0; dw < (g.stem_unfolded ? 1 : g.kw); ++dw) {
+        ++tap_index;
+        if (!tap_live(dt, g.pt, g.st, g.Ti, g.To) || !tap_live(dh, g.ph, g.sh, g.Hi, g.Ho) ||
+            (!g.stem_unfolded && !tap_live(dw, g.pw, g.sw, g.Wi, g.Wo)))
+          continue;
         if (ntap >= kMaxTaps) {
           if (err) *err = "conv_tc: too many filter taps";
           return false;
@@ -245,7 +302,7 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
         p.tap_dh[ntap] = (int8_t)sh_;
         p.tap_dt[ntap] = (int8_t)st_;
         p.tap_coff[ntap] = 0;
-        p.tap_koff[ntap] = ntap * cp;
+        p.tap_koff[ntap] = tap_index * cp;
         ++ntap;
       }
   p.num_taps = ntap;
@@ -270,14 +327,15 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
     const uint64_t strides[4] = {(uint64_t)eff_sw * in_c * 2, (uint64_t)g.sh * in_w * in_c * 2,
                                  (uint64_t)g.st * g.Hi * in_w * in_c * 2,
                                  (uint64_t)g.Ti * g.Hi * in_w * in_c * 2};
-    const uint32_t box[5] = {(uint32_t)p.bk, (uint32_t)bw, (uint32_t)bh, (uint32_t)bt, (uint32_t)bb};
+    uint32_t box[5] = {(uint32_t)p.bk, (uint32_t)bw, (uint32_t)bh, (uint32_t)bt, (uint32_t)bb};
+    box[1 + p.a_slice_dim] /= (uint32_t)p.cn;  // every CTA of a cluster row fetches one slice
     if (!encode_bf16(&p.a_map[v], base, 5, dims, strides, box, swz, err)) return false;
   }
   for (size_t v = views.size(); v < 4; ++v) p.a_map[v] = p.a_map[0];
   {
     const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)np};
     const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
-    const uint32_t box[2] = {(uint32_t)p.bk, (uint32_t)p.block_n};
+    const uint32_t box[2] = {(uint32_t)p.bk, (uint32_t)(p.block_n / p.cm)};
     if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, swz, err)) return false;
   }
   p.y = y;

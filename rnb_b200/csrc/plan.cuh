@@ -46,9 +46,12 @@ void pack_conv_weights_ref(const ConvGeom& g, const float* w, std::vector<float>
 
 // Fill `out` for a batch of B clips.  All pointers are device pointers.  Returns false and sets
 // *err on failure (unsupported geometry or a tensor-map encoding error).
+// force_cm/force_cn > 0 pin the cluster shape (falling back to 1 x 1 when the geometry cannot be
+// split that way); 0 lets the traffic model choose.
 bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
-                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift, const __nv_bfloat16* residual, bool relu, int num_sms,
-                          ConvTcParams* out, std::string* err);
+                          const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
+                          const __nv_bfloat16* residual, bool relu, int num_sms, ConvTcParams* out,
+                          std::string* err, int force_cm = 0, int force_cn = 0);
 
 // Patch kernel (conv_patch.cuh): applicable to stride-1 1x3x3 and 3x1x1 convolutions whose packed
 // weights fit in shared memory next to two activation patches.

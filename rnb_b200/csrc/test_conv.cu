@@ -149,10 +149,10 @@ static bool run_case(const Case& c, int perf_iters) {
   const double rel = max_err / (max_ref > 0 ? max_ref : 1);
   const bool pass = rel < 1e-2 && bad_pad == 0;
   const int bw = 1 << tp.lbw, bh = 1 << tp.lbh, bt = 1 << tp.lbt;
-  printf("%-28s B=%-2d box(w%d h%d t%d b%d) N=%dx%d stages=%d taps=%d  max|ref|=%.3f max|err|=%.4f "
-         "rel=%.2e pad_bad=%zu worst@%zu  %s\n",
+  printf("%-28s B=%-2d box(w%d h%d t%d b%d) N=%dx%d stages=%d taps=%d cluster=%dx%d  max|ref|=%.3f "
+         "max|err|=%.4f rel=%.2e pad_bad=%zu worst@%zu  %s\n",
          c.name, B, bw, bh, bt, 128 / (bw * bh * bt), tp.n_tiles, tp.block_n, tp.num_stages,
-         tp.num_taps, max_ref, max_err, rel, bad_pad, worst, pass ? "PASS" : "FAIL");
+         tp.num_taps, tp.cm, tp.cn, max_ref, max_err, rel, bad_pad, worst, pass ? "PASS" : "FAIL");
 
   // ---- the patch kernel on the same problem, with both descriptor base-offset conventions
   bool patch_pass = true;
