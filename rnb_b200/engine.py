@@ -263,3 +263,54 @@ class R2P1DEngine:
             ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(self._sum.data_ptr()),
             ctypes.c_void_p(self._cls.data_ptr()), ctypes.c_void_p(stream)))
         return out, self._sum, self._cls
+
+
+class HostPipeline:
+    """Feeds an engine from pinned host memory, end to end: host uint8 frames in, host logits out.
+
+    The host->device copy of batch i+1 runs on a copy stream while batch i is in the network
+    (double-buffered device inputs, CUDA events in both directions); the logits go back to pinned
+    host memory on the compute stream.  This is the serving loop a caller without device-resident
+    data uses -- RnB's loader hands device tensors to the runner, so there the copy does not exist.
+    """
+
+    def __init__(self, engine, batch, depth=2):
+        self.engine = engine
+        self.depth = depth
+        dev = engine.device
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.dev_in = [torch.empty((batch, 8, 3, 112, 112), dtype=torch.uint8, device=dev)
+                       for _ in range(depth)]
+        self.host_out = [torch.empty((batch,) + engine.out_shape, dtype=torch.float32).pin_memory()
+                         for _ in range(depth)]
+        self.in_ready = [torch.cuda.Event() for _ in range(depth)]
+        self.in_free = [torch.cuda.Event() for _ in range(depth)]
+        self.out_ready = [torch.cuda.Event() for _ in range(depth)]
+        self.count = 0
+        self.h2d_bytes = self.dev_in[0].numel()
+        self.d2h_bytes = self.host_out[0].numel() * 4
+
+    def submit(self, host_frames):
+        """Queue one batch (pinned uint8 (B, 8, 3, 112, 112)); returns the slot its logits land in.
+
+        ``result(slot)`` waits for them.  At most ``depth`` batches may be outstanding.
+        """
+        slot = self.count % self.depth
+        compute = torch.cuda.current_stream(self.engine.device)
+        n = host_frames.shape[0]
+        with torch.cuda.stream(self.copy_stream):
+            if self.count >= self.depth:
+                self.copy_stream.wait_event(self.in_free[slot])
+            self.dev_in[slot][:n].copy_(host_frames, non_blocking=True)
+            self.in_ready[slot].record(self.copy_stream)
+        compute.wait_event(self.in_ready[slot])
+        logits = self.engine(self.dev_in[slot][:n])
+        self.in_free[slot].record(compute)
+        self.host_out[slot][:n].copy_(logits, non_blocking=True)
+        self.out_ready[slot].record(compute)
+        self.count += 1
+        return slot
+
+    def result(self, slot):
+        self.out_ready[slot].synchronize()
+        return self.host_out[slot]

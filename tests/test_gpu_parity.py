@@ -353,3 +353,21 @@ def test_peer_copy_across_gpus(lib):
     got = handoff.fetch(placeholder, shared, n)                # consumer pulls it back
     assert n == 5 and torch.equal(got, src[:5])
     assert torch.equal(shared[:5].cpu(), src[:5].cpu())
+
+
+def test_host_pipeline_end_to_end(engines, models):
+    """Pinned host frames in, host logits out, copies overlapped with compute: same numbers."""
+    from rnb_b200.engine import HostPipeline
+    eng = engines('bf16', True)
+    pipe = HostPipeline(eng, batch=4)
+    batches = [R.synthetic_clips(4, seed=200 + i).pin_memory() for i in range(5)]
+    slots, outs = [], []
+    for i, hb in enumerate(batches):
+        slot = pipe.submit(hb)
+        if i >= 1:                       # keep one batch in flight, like a serving loop
+            outs.append(pipe.result(slots[-1]).clone())
+        slots.append(slot)
+    outs.append(pipe.result(slots[-1]).clone())
+    for hb, got in zip(batches, outs):
+        want = R.forward_u8(models[True], hb)
+        check_logits(got, want, 'bf16')
