@@ -1,13 +1,17 @@
-// "Patch" variant of the tcgen05 convolution for stride-1 layers whose weights fit in shared memory.
+// "Patch" variant of the tcgen05 convolution for stride-1 1x3x3 and 3x1x1 layers.
 //
-// conv_tc_kernel re-reads the 128-row activation tile once per filter tap and streams the weights
-// through shared memory for every tile, so its L2->SM traffic is ~taps x (A + B) per tile (983 MB
-// per conv2 launch, profiles/r01_ncu_conv_tc_v1.md).  Here the CTA loads ALL packed weights once,
-// and per tile ONE activation patch (tile + halo); every filter tap is the same patch read at a row
+// conv_tc_kernel re-reads the 128-row activation tile once per filter tap, so an SM has to pull
+// taps x (A + B) bytes per tile through its ~68 B/clk inbound port (983 MB L2->SM per conv2 launch,
+// profiles/r01_ncu_conv_tc_v1.md) -- that port, not the tensor core, bounds it.  Here a CTA loads
+// ONE activation patch (tile + halo) per tile and every filter tap is the same patch read at a row
 // offset, expressed only in the UMMA shared-memory descriptor.  (Measured on B200: the 128-byte
 // swizzle is a function of the shared-memory ADDRESS bits, so a descriptor whose start address is
 // shifted by whole 128-byte rows reads correctly with the base-offset field left at zero; filling
 // that field with address bits 7-9 gives wrong results.  profiles/r01_test_conv_patch.log)
+//
+// Weights: RESIDENT mode keeps all packed weights in shared memory for the life of the CTA (conv2
+// stage, stem temporal); STREAM mode (weights too large) tiles the output channels and streams the
+// weight tiles of one channel tile through a ring, once per (position tile, channel tile).
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -18,11 +22,12 @@
 
 namespace rnb {
 
-constexpr int kPatchMaxKb = 4;  // 64-channel blocks per patch
+constexpr int kPatchMaxKb = 4;      // 64-channel blocks per patch
+constexpr int kPatchMaxBStages = 8;
 
 struct ConvPatchParams {
   alignas(64) CUtensorMap a_map;  // activation (C, W, H, T, B), box (64, pbox_w, pbox_h, pbox_t, 1)
-  alignas(64) CUtensorMap b_map;  // packed weights (K_total, N), box (64, N)
+  alignas(64) CUtensorMap b_map;  // packed weights (K_total, N), box (64, block_n)
   const float* shift;
   const __nv_bfloat16* residual;
   __nv_bfloat16* y;     // output (B, To, Ho, Wo, cout_pad): written with plain 32-byte stores
@@ -30,7 +35,9 @@ struct ConvPatchParams {
   int cin_pad;
   int patch_rows;       // rows (positions) of one patch block = pbox_w * pbox_h * pbox_t
   int num_taps;
-  int n;                // output channels = accumulator columns (multiple of 16, <= 256)
+  int n;                // output channels (multiple of 16)
+  int n_tiles, block_n; // channel tiling: resident mode has one tile of n channels
+  int b_stages;         // 0: weights resident; > 0: ring depth of the streamed weight tiles
   // output tile: tw x th x tt positions, laid out in the accumulator with power-of-two pitches
   int tw, th, tt;
   int lpw, lph;         // log2 of the row pitches: row = (t << (lpw + lph)) + (h << lpw) + w
@@ -39,12 +46,12 @@ struct ConvPatchParams {
   int Wo, Ho, To, B;
   int cout_pad;
   int relu;
-  long long* dbg;       // optional: 8 cycle counters per CTA (see conv_patch.cu), or nullptr
   int16_t tap_shift[kMaxTaps];  // row offset of each tap inside the patch
 };
 
-inline int conv_patch_smem_bytes(int nkb, int patch_rows, int num_taps, int n) {
-  return 1024 + num_taps * nkb * n * 128 + 2 * nkb * patch_rows * 128 + 1024 /*slack rows*/ + 256 +
+inline int conv_patch_smem_bytes(int nkb, int patch_rows, int num_taps, int block_n, int b_stages) {
+  const int wtiles = b_stages > 0 ? b_stages : num_taps * nkb;
+  return 1024 + wtiles * block_n * 128 + 2 * nkb * patch_rows * 128 + 1024 /*slack rows*/ + 256 +
          kMaxBlockN * 4;
 }
 

@@ -9,6 +9,7 @@
 #include "model.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/rnb_b200.h"
@@ -429,50 +430,84 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
         __nv_bfloat16* y = (__nv_bfloat16*)slots_[op.out_slot];
         const __nv_bfloat16* res =
             op.res_slot >= 0 ? (const __nv_bfloat16*)slots_[op.res_slot] : nullptr;
-        plan[i].patch = conv_patch_applicable(op.g);
-        bool ok;
-        if (plan[i].patch) {
-          ok = build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &plan[i].pp,
-                                       &perr);
-        } else {
-          // Which cluster shape is fastest depends on the layer (it trades L2 reads against
-          // lock-step between CTAs), so time the candidates once per (layer, batch size) -- the
-          // reference runs with cudnn.benchmark = True for the same reason (runner.py:25).
+        // Candidates: the patch kernel (always taken when its weights are resident), and the tap
+        // kernel in each cluster shape.  Which is fastest depends on the layer (shared-memory
+        // bandwidth vs. tile fit vs. lock-step between CTAs), so time them once per (layer, batch
+        // size) -- the reference runs with cudnn.benchmark = True for the same reason
+        // (runner.py:25).
+        // RNB_B200_PATCH_STREAM=0 keeps streamed-weight patch launches out of the candidate set
+        static const bool allow_stream = [] {
+          const char* e = getenv("RNB_B200_PATCH_STREAM");
+          return !(e && e[0] == '0');
+        }();
+        const bool patch_ok =
+            conv_patch_applicable(op.g) && (allow_stream || !conv_patch_streams(op.g));
+        const bool patch_only = patch_ok && !conv_patch_streams(op.g);
+        bool ok = false;
+        float best_ms = -1.f;
+        cudaEvent_t e0, e1;
+        if (!cuda_ok(cudaEventCreate(&e0), "cudaEventCreate", err) ||
+            !cuda_ok(cudaEventCreate(&e1), "cudaEventCreate", err))
+          return RNB_ECUDA;
+        auto time_it = [&](auto&& launch, float* ms) -> bool {
+          cudaError_t te = launch();
+          if (te == cudaSuccess) te = cudaEventRecord(e0, stream);
+          for (int r = 0; r < 8 && te == cudaSuccess; ++r) te = launch();
+          if (te == cudaSuccess) te = cudaEventRecord(e1, stream);
+          if (te == cudaSuccess) te = cudaEventSynchronize(e1);
+          if (te == cudaSuccess) te = cudaEventElapsedTime(ms, e0, e1);
+          if (te != cudaSuccess) perr = std::string("plan timing: ") + cudaGetErrorString(te);
+          return te == cudaSuccess;
+        };
+        bool failed = false;
+        if (patch_ok) {
+          ConvPatchParams trial;
+          if (!build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &trial,
+                                       &perr)) {
+            failed = true;
+          } else if (patch_only) {
+            plan[i].patch = true;
+            plan[i].pp = trial;
+            ok = true;
+          } else {
+            float ms = 0.f;
+            if (!time_it([&] { return launch_conv_patch(trial, num_sms_, stream); }, &ms)) {
+              failed = true;
+            } else {
+              best_ms = ms;
+              plan[i].patch = true;
+              plan[i].pp = trial;
+              ok = true;
+            }
+          }
+        }
+        if (!patch_only && !failed) {
           static const int cand[6][2] = {{1, 1}, {2, 1}, {4, 1}, {1, 2}, {2, 2}, {1, 4}};
-          float best_ms = -1.f;
-          ok = false;
-          cudaEvent_t e0, e1;
-          if (!cuda_ok(cudaEventCreate(&e0), "cudaEventCreate", err) ||
-              !cuda_ok(cudaEventCreate(&e1), "cudaEventCreate", err))
-            return RNB_ECUDA;
           for (const auto& c : cand) {
             ConvTcParams trial;
             if (!build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_,
-                                      &trial, &perr, c[0], c[1]))
-              break;
-            if (trial.cm != c[0] || trial.cn != c[1]) continue;  // shape not applicable here
-            float ms = 0.f;
-            cudaError_t te = launch_conv_tc(trial, num_sms_, stream);
-            if (te == cudaSuccess) te = cudaEventRecord(e0, stream);
-            for (int r = 0; r < 8 && te == cudaSuccess; ++r) te = launch_conv_tc(trial, num_sms_, stream);
-            if (te == cudaSuccess) te = cudaEventRecord(e1, stream);
-            if (te == cudaSuccess) te = cudaEventSynchronize(e1);
-            if (te == cudaSuccess) te = cudaEventElapsedTime(&ms, e0, e1);
-            if (te != cudaSuccess) {
-              perr = std::string("cluster autotune: ") + cudaGetErrorString(te);
-              ok = false;
+                                      &trial, &perr, c[0], c[1])) {
+              failed = true;
               break;
             }
-            // leave the plain 1 x 1 launch only for a clear win
+            if (trial.cm != c[0] || trial.cn != c[1]) continue;  // shape not applicable here
+            float ms = 0.f;
+            if (!time_it([&] { return launch_conv_tc(trial, num_sms_, stream); }, &ms)) {
+              failed = true;
+              break;
+            }
+            // leave the earlier (simpler) candidate only for a clear win
             if (best_ms < 0 || ms < best_ms * 0.97f) {
               best_ms = ms;
+              plan[i].patch = false;
               plan[i].tc = trial;
               ok = true;
             }
           }
-          cudaEventDestroy(e0);
-          cudaEventDestroy(e1);
         }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        if (failed) ok = false;
         if (!ok) {
           if (err) *err = op.name + ": " + perr;
           return RNB_ECUDA;

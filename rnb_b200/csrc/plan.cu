@@ -349,41 +349,93 @@ struct PatchShape {
   int nkb = 0, patch_rows = 0, taps = 0;
   int tw = 0, th = 0, tt = 0, lpw = 0, lph = 0;
   int pbw = 0, pbh = 0, pbt = 0;  // patch box extent
+  int n_tiles = 1, block_n = 0, b_stages = 0;
+  double eff = 0;
 };
+
+int ilog2(int v) {
+  int l = 0;
+  while ((1 << l) < v) ++l;
+  return l;
+}
 
 PatchShape patch_shape(const ConvGeom& g) {
   PatchShape s;
   if (g.stem_unfolded || g.st != 1 || g.sh != 1 || g.sw != 1) return s;
-  if (g.cout_pad() > kMaxBlockN) return s;
   s.nkb = ceil_div(g.cin_pad(), 64);
   if (s.nkb > kPatchMaxKb) return s;
+  const int np = g.cout_pad();
   if (g.kt == 1 && g.kh == 3 && g.kw == 3 && g.ph == 1 && g.pw == 1 && g.pt == 0) {
-    // one frame, 8 rows of 14 columns; accumulator rows use a pitch of 16 so that a filter tap is
-    // a pure row offset (dh * 16 + dw) inside the 10 x 16 patch
+    // One frame per tile.  Accumulator rows use a power-of-two pitch that also holds the two halo
+    // columns, so that a filter tap is a pure row offset (dh * pitch + dw) inside the patch.
     s.spatial = true;
     s.taps = 9;
-    s.tw = 14; s.th = 8; s.tt = 1; s.lpw = 4; s.lph = 3;
-    s.pbw = 16; s.pbh = 10; s.pbt = 1;
-  } else if (g.kt == 3 && g.kh == 1 && g.kw == 1 && g.pt == 1 && g.ph == 0 && g.pw == 0) {
-    // 16 positions (8 x 2) by up to 8 frames; a tap is an offset of 16 rows in the 10-frame patch
+    for (int pitch : {16, 32}) {
+      const int th = 128 / pitch;
+      const int tiles_w = ceil_div(g.Wo, pitch - 2);
+      const int tw = ceil_div(g.Wo, tiles_w);
+      const double eff = (double)g.Wo * g.Ho / ((double)tiles_w * ceil_div(g.Ho, th) * 128);
+      if (eff > s.eff) {
+        s.eff = eff;
+        s.tw = tw; s.th = th; s.tt = 1; s.lpw = ilog2(pitch); s.lph = ilog2(th);
+        s.pbw = pitch; s.pbh = th + 2; s.pbt = 1;
+      }
+    }
+  } else if (g.kt == 3 && g.kh == 1 && g.kw == 1 && g.pt == 1 && g.ph == 0 && g.pw == 0 &&
+             g.To >= 2) {
+    // tt frames of P = 128 / tt positions; a tap is an offset of P rows in the (tt + 2)-frame patch
     s.taps = 3;
-    s.tw = 8; s.th = 2; s.tt = g.To < 8 ? g.To : 8; s.lpw = 3; s.lph = 1;
-    s.pbw = 8; s.pbh = 2; s.pbt = s.tt + 2;
+    const int tt = g.To >= 8 ? 8 : (g.To >= 4 ? 4 : 2);
+    const int P = 128 / tt;
+    for (int pw = 8; pw <= P && pw <= 64; pw *= 2) {
+      const int ph = P / pw;
+      const int tiles_w = ceil_div(g.Wo, pw);
+      const int tw = ceil_div(g.Wo, tiles_w);
+      const int tiles_h = ceil_div(g.Ho, ph);
+      const double eff = (double)g.Wo * g.Ho * g.To /
+                         ((double)tiles_w * tiles_h * ceil_div(g.To, tt) * 128);
+      if (eff > s.eff) {
+        s.eff = eff;
+        s.tw = tw; s.th = ph; s.tt = tt; s.lpw = ilog2(pw); s.lph = ilog2(ph);
+        s.pbw = pw; s.pbh = ph; s.pbt = tt + 2;
+      }
+    }
   } else {
     return s;
   }
-  s.patch_rows = s.pbw * s.pbh * s.pbt;
-  if (conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, g.cout_pad()) > kSmemLimit) return s;
   // ragged tiles are legal (stores are masked) but waste tensor work; require a reasonable fit
-  const double eff = (double)g.Wo * g.Ho * g.To /
-                     ((double)ceil_div(g.Wo, s.tw) * ceil_div(g.Ho, s.th) * ceil_div(g.To, s.tt) * 128);
-  if (eff < 0.6) return s;
-  s.ok = true;
+  if (s.eff < 0.6) return s;
+  s.patch_rows = s.pbw * s.pbh * s.pbt;
+  // weights resident if they fit next to two patches, otherwise streamed per channel tile
+  if (np <= kMaxBlockN && conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np, 0) <= kSmemLimit) {
+    s.n_tiles = 1;
+    s.block_n = np;
+    s.b_stages = 0;
+    s.ok = true;
+    return s;
+  }
+  for (int nt = ceil_div(np, kMaxBlockN); nt <= 8; ++nt) {
+    const int bn = round_up(ceil_div(np, nt), 16);
+    const int fixed = conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, bn, 1) - bn * 128;
+    int stages = (kSmemLimit - fixed) / (bn * 128);
+    if (stages > kPatchMaxBStages) stages = kPatchMaxBStages;
+    if (stages >= 4 && bn >= 64) {
+      s.n_tiles = ceil_div(np, bn);
+      s.block_n = bn;
+      s.b_stages = stages;
+      s.ok = true;
+      return s;
+    }
+  }
   return s;
 }
 }  // namespace
 
 bool conv_patch_applicable(const ConvGeom& g) { return patch_shape(g).ok; }
+bool conv_patch_streams(const ConvGeom& g) {
+  const PatchShape s = patch_shape(g);
+  return s.ok && s.b_stages > 0;
+}
 
 bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                              const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
@@ -405,6 +457,9 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   p.patch_rows = s.patch_rows;
   p.num_taps = s.taps;
   p.n = np;
+  p.n_tiles = s.n_tiles;
+  p.block_n = s.block_n;
+  p.b_stages = s.b_stages;
   p.tw = s.tw; p.th = s.th; p.tt = s.tt;
   p.lpw = s.lpw; p.lph = s.lph;
   p.tiles_w = ceil_div(g.Wo, s.tw);
@@ -429,7 +484,7 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   {
     const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)np};
     const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
-    const uint32_t box[2] = {64u, (uint32_t)np};
+    const uint32_t box[2] = {64u, (uint32_t)s.block_n};
     if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, 128, err)) return false;
   }
   return true;

@@ -56,6 +56,9 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
 // Patch kernel (conv_patch.cuh): applicable to stride-1 1x3x3 and 3x1x1 convolutions whose packed
 // weights fit in shared memory next to two activation patches.
 bool conv_patch_applicable(const ConvGeom& g);
+// true when the patch kernel would have to stream its weights (they do not fit in shared memory);
+// then the tap kernel may be faster and the model times both
+bool conv_patch_streams(const ConvGeom& g);
 bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                              const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                              const __nv_bfloat16* residual, bool relu, ConvPatchParams* out,

@@ -182,25 +182,10 @@ static bool run_case(const Case& c, int perf_iters) {
           if (!(e <= perr)) perr = e;
         }
       const bool ok = perr / (max_ref > 0 ? max_ref : 1) < 1e-2 && pbad == 0 && nanc == 0;
-      printf("    patch kernel: max|err|=%.4f pad_bad=%zu nan=%zu  %s\n", perr, pbad, nanc,
+      printf("    patch kernel (tile w%d h%d t%d, N=%dx%d, %s): max|err|=%.4f pad_bad=%zu nan=%zu  %s\n",
+             pp.tw, pp.th, pp.tt, pp.n_tiles, pp.block_n,
+             pp.b_stages ? "streamed weights" : "resident weights", perr, pbad, nanc,
              ok ? "PASS" : "FAIL");
-      if (ok && perf_iters > 0 && mode == 0) {
-        long long* ddbg;
-        CK(cudaMalloc(&ddbg, 148 * 8 * 8));
-        CK(cudaMemset(ddbg, 0, 148 * 8 * 8));
-        pp.dbg = ddbg;
-        CK(launch_conv_patch(pp, num_sms, 0));
-        CK(cudaDeviceSynchronize());
-        long long h[148 * 8];
-        CK(cudaMemcpy(h, ddbg, sizeof h, cudaMemcpyDeviceToHost));
-        pp.dbg = nullptr;
-        cudaFree(ddbg);
-        for (int b : {0, 73, 147})
-          printf("    cta %3d: tiles %lld | producer wait p_empty %lld | mma wait weights %lld, tmem_empty %lld, "
-                 "p_full %lld, total %lld | epi wait tmem_full %lld, total %lld (cycles)\n",
-                 b, h[b * 8 + 5], h[b * 8 + 0], h[b * 8 + 1], h[b * 8 + 2], h[b * 8 + 3], h[b * 8 + 4],
-                 h[b * 8 + 6], h[b * 8 + 7]);
-      }
       if (ok && perf_iters > 0) {
         cudaEvent_t e0, e1;
         CK(cudaEventCreate(&e0));
