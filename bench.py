@@ -26,6 +26,7 @@ LAYER_SIZES = {'r18': [2, 2, 2, 2, 2], 'r34': [2, 3, 4, 6, 3]}  # runner form: s
 GFLOP_PER_CLIP = {'r18': 42.172, 'r34': 76.853}
 METRIC = 'R(2+1)D clips/sec (8x112x112 clips)'
 CLIP_BYTES = 8 * 3 * 112 * 112
+NCU_DRAM_BYTES_PER_CONV_LAUNCH = 42.6e6  # profiles/r01_ncu_launches_v2.md (1705.6 MB / 40 launches)
 FALLBACK_PEAK_TFLOPS = 1590.0  # /opt/skills/guides/B200_PROFILING.md, used only without MEASURED_PEAKS.json
 
 
@@ -207,6 +208,10 @@ def run_b200(args, rank, world, local_rank):
         engine(pool[i % pool_n])
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # lets `ncu --profile-from-start off` capture exactly the timed steps (never used for a number)
+    mark_profile = os.environ.get('RNB_BENCH_CUDA_PROFILER') == '1'
+    if mark_profile:
+        torch.cuda.profiler.start()
     t_wall0 = time.time()
     ev0.record()
     for i in range(K):
@@ -214,6 +219,8 @@ def run_b200(args, rank, world, local_rank):
     ev1.record()
     barrier()
     t_wall1 = time.time()
+    if mark_profile:
+        torch.cuda.profiler.stop()
     value, ms = rdist.whole_job_throughput(K * B, ev0.elapsed_time(ev1), dev)
     clocks = sampler.summary(t_wall0, t_wall1)
 
@@ -308,7 +315,14 @@ def run_b200(args, rank, world, local_rank):
         'gpu_launches': K * engine.num_launches,
         'clocks': clocks,
         'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak_burst,
-                     'unit': 'TFLOP/s', 'frac': achieved / peak_burst, 'traffic': None,
+                     'unit': 'TFLOP/s', 'frac': achieved / peak_burst,
+                     # dram__bytes_read + write per convolution launch (average over the 40 launches
+                     # of one step), ncu capture in profiles/r01_ncu_launches_v2.md; only valid for
+                     # the configuration that capture was taken on
+                     'traffic': NCU_DRAM_BYTES_PER_CONV_LAUNCH
+                     if (args.model, args.dtype, B, world) == ('r18', 'bf16', 16, 1) else None,
+                     'traffic_unit': 'bytes',
+                     'algorithmic_bytes_per_launch': sum(a * B + w for _, _, a, w, _ in info) / n_conv,
                      'kernel': 'tcgen05 implicit-GEMM convolutions: conv_tc_kernel + '
                                'conv_patch_kernel (%d launches per step)' % n_conv,
                      'by_kernel': by_kernel,
