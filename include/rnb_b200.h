@@ -85,16 +85,19 @@ int rnb_r2p1d_classify(void* handle, const void* in, int in_fmt, int batch, floa
 int rnb_r2p1d_io_shape(void* handle, int which, int64_t shape4[4]);
 
 /* Bookkeeping for benchmarks (no counterpart in the reference): algorithmic FLOPs of one forward
- * over `batch` clips (2 x MACs of every convolution and the classifier) and the number of kernels
- * one forward launches. */
+ * over `batch` clips (2 x MACs of every convolution and the classifier), the number of kernels the
+ * most recent forward launched (a convolution may run in several batch chunks, RNB_B200_CHUNK_MB),
+ * and the number of convolutions (Conv3d modules) in the layer range. */
 double rnb_r2p1d_flops(void* handle, int batch);
 int rnb_r2p1d_num_launches(void* handle);
+int rnb_r2p1d_num_convs(void* handle);
 
 /* Diagnostics for bench.py and profiles/ (no counterpart in the reference, which times steps with
  * wall-clock TimeCards only): the same forward pass with a CUDA event recorded on
- * `stream` between consecutive kernels.  ms[0] = input staging, ms[1 .. n_ops] = the convolutions
- * in launch order, ms[n_ops + 1] = pool + classifier (or the output layout change); `cap` is the
- * capacity of ms and must be >= rnb_r2p1d_num_launches().  Synchronises `stream` before returning.
+ * `stream` between consecutive kernels.  With n = rnb_r2p1d_num_convs(): ms[0] = input staging,
+ * ms[1 .. n] = the convolutions in module order (launches of one convolution summed), ms[n + 1] =
+ * pool + classifier (or the output layout change); `cap` is the capacity of ms and must be
+ * >= n + 2.  Synchronises `stream` before returning.
  * rnb_r2p1d_op_info() describes convolution `op` (0-based): its state_dict prefix, algorithmic
  * FLOPs per clip, and the bytes per clip it must move at least once (input + output + residual
  * activations in the handle's dtype; weights are per batch and reported separately), and which

@@ -56,6 +56,7 @@ PROTOTYPES = {
     'rnb_r2p1d_io_shape': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _c_i64_p]),
     'rnb_r2p1d_flops': (ctypes.c_double, [ctypes.c_void_p, ctypes.c_int]),
     'rnb_r2p1d_num_launches': (ctypes.c_int, [ctypes.c_void_p]),
+    'rnb_r2p1d_num_convs': (ctypes.c_int, [ctypes.c_void_p]),
     'rnb_r2p1d_destroy': (None, [ctypes.c_void_p]),
     'rnb_preprocess_u8': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _c_f32_p, _c_f32_p,
                                          ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),

@@ -210,6 +210,12 @@ int rnb_r2p1d_num_launches(void* handle) {
   return m->num_launches();
 }
 
+int rnb_r2p1d_num_convs(void* handle) {
+  auto* m = static_cast<rnb::R2P1DModel*>(handle);
+  if (!m || !m->finalized()) return fail(RNB_ESTATE, "handle not finalized");
+  return m->num_ops();
+}
+
 void rnb_r2p1d_destroy(void* handle) { delete static_cast<rnb::R2P1DModel*>(handle); }
 
 int rnb_preprocess_u8(const uint8_t* in, int batch, const float* scale3, const float* bias3,

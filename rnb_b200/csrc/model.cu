@@ -359,28 +359,201 @@ bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
 
 int R2P1DModel::profile(const void* in, int in_fmt, int batch, void* out, int out_fmt,
                         cudaStream_t stream, float* ms, int cap, std::string* err) {
-  const int n = num_launches();
-  if (!ms || cap < n) {
+  const int n_ops = (int)ops_.size();
+  if (!ms || cap < n_ops + 2) {
     if (err) *err = "profile: ms buffer too small";
     return RNB_EINVAL;
   }
+  // one event per kernel; a chunked convolution's launches are summed into its entry
+  std::vector<int> launch_op;
+  if (dtype_ == RNB_DTYPE_BF16 && batch > 0 && batch <= max_batch_) {
+    const std::vector<Launch>* plan = ensure_plan(batch, stream, err);
+    if (!plan) return RNB_ECUDA;
+    for (const Launch& l : *plan) launch_op.push_back(l.op);
+  } else {
+    for (int i = 0; i < n_ops; ++i) launch_op.push_back(i);
+  }
+  const int n = (int)launch_op.size() + 2;
   std::vector<cudaEvent_t> ev(n + 1, nullptr);
   for (auto& e : ev)
     if (!cuda_ok(cudaEventCreate(&e), "cudaEventCreate", err)) return RNB_ECUDA;
   int rc = forward(in, in_fmt, batch, out, out_fmt, stream, err, ev.data());
   if (rc == RNB_OK && !cuda_ok(cudaStreamSynchronize(stream), "profile sync", err)) rc = RNB_ECUDA;
-  if (rc == RNB_OK) {
+  for (int i = 0; i < n_ops + 2; ++i) ms[i] = 0.f;
+  if (rc == RNB_OK && batch > 0) {
     for (int i = 0; i < n; ++i) {
-      ms[i] = 0.f;
-      if (batch > 0 && !cuda_ok(cudaEventElapsedTime(&ms[i], ev[i], ev[i + 1]), "elapsed", err)) {
+      float t = 0.f;
+      if (!cuda_ok(cudaEventElapsedTime(&t, ev[i], ev[i + 1]), "elapsed", err)) {
         rc = RNB_ECUDA;
         break;
       }
+      const int slot = i == 0 ? 0 : (i == n - 1 ? n_ops + 1 : 1 + launch_op[i - 1]);
+      ms[slot] += t;
     }
   }
   for (auto& e : ev)
     if (e) cudaEventDestroy(e);
   return rc;
+}
+
+// Plans one launch.  With `like` the kernel choice (patch vs tap kernel, cluster shape) is copied
+// from an already planned launch of the same layer; otherwise the candidates are timed -- which is
+// fastest depends on the layer (shared-memory bandwidth vs. tile fit vs. lock-step between CTAs),
+// and the reference runs with cudnn.benchmark = True for the same reason (runner.py:25).
+bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cudaStream_t stream,
+                           const Launch* like, Launch* out, std::string* err) {
+  const ConvOp& op = ops_[op_index];
+  // a chunked spatial->temporal pair reuses the START of the intermediate slot for every chunk
+  const size_t in_off = (chunked && op.in_slot == SLOT_M) ? 0 : (size_t)first * op.g.in_elems(1);
+  const size_t out_off = (chunked && op.out_slot == SLOT_M) ? 0 : (size_t)first * op.g.out_elems(1);
+  const __nv_bfloat16* x = (const __nv_bfloat16*)slots_[op.in_slot] + in_off;
+  const __nv_bfloat16* w = (const __nv_bfloat16*)op.d_w;
+  __nv_bfloat16* y = (__nv_bfloat16*)slots_[op.out_slot] + out_off;
+  const __nv_bfloat16* res =
+      op.res_slot >= 0 ? (const __nv_bfloat16*)slots_[op.res_slot] + out_off : nullptr;
+  out->op = op_index;
+  out->first = first;
+  out->batch = batch;
+  std::string perr;
+  auto fail = [&](const std::string& m) {
+    if (err) *err = op.name + ": " + m;
+    return false;
+  };
+  if (like) {
+    out->patch = like->patch;
+    const bool ok = like->patch
+                        ? build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
+                                                  &out->pp, &perr)
+                        : build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
+                                               num_sms_, &out->tc, &perr, like->tc.cm, like->tc.cn);
+    return ok ? true : fail(perr);
+  }
+  // RNB_B200_PATCH_STREAM=0 keeps streamed-weight patch launches out of the candidate set
+  static const bool allow_stream = [] {
+    const char* e = getenv("RNB_B200_PATCH_STREAM");
+    return !(e && e[0] == '0');
+  }();
+  const bool patch_ok = conv_patch_applicable(op.g) && (allow_stream || !conv_patch_streams(op.g));
+  const bool patch_only = patch_ok && !conv_patch_streams(op.g);
+  if (patch_only) {
+    out->patch = true;
+    return build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &out->pp, &perr)
+               ? true
+               : fail(perr);
+  }
+  cudaEvent_t e0, e1;
+  if (!cuda_ok(cudaEventCreate(&e0), "cudaEventCreate", err) ||
+      !cuda_ok(cudaEventCreate(&e1), "cudaEventCreate", err))
+    return false;
+  auto time_it = [&](auto&& launch, float* ms) -> bool {
+    cudaError_t te = launch();
+    if (te == cudaSuccess) te = cudaEventRecord(e0, stream);
+    for (int r = 0; r < 8 && te == cudaSuccess; ++r) te = launch();
+    if (te == cudaSuccess) te = cudaEventRecord(e1, stream);
+    if (te == cudaSuccess) te = cudaEventSynchronize(e1);
+    if (te == cudaSuccess) te = cudaEventElapsedTime(ms, e0, e1);
+    if (te != cudaSuccess) perr = std::string("plan timing: ") + cudaGetErrorString(te);
+    return te == cudaSuccess;
+  };
+  bool ok = false, failed = false;
+  float best_ms = -1.f;
+  if (patch_ok) {
+    ConvPatchParams trial;
+    float ms = 0.f;
+    if (!build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &trial, &perr) ||
+        !time_it([&] { return launch_conv_patch(trial, num_sms_, stream); }, &ms)) {
+      failed = true;
+    } else {
+      best_ms = ms;
+      out->patch = true;
+      out->pp = trial;
+      ok = true;
+    }
+  }
+  static const int cand[6][2] = {{1, 1}, {2, 1}, {4, 1}, {1, 2}, {2, 2}, {1, 4}};
+  for (int ci = 0; ci < 6 && !failed; ++ci) {
+    ConvTcParams trial;
+    if (!build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &trial,
+                              &perr, cand[ci][0], cand[ci][1])) {
+      failed = true;
+      break;
+    }
+    if (trial.cm != cand[ci][0] || trial.cn != cand[ci][1]) continue;  // shape not applicable
+    float ms = 0.f;
+    if (!time_it([&] { return launch_conv_tc(trial, num_sms_, stream); }, &ms)) {
+      failed = true;
+      break;
+    }
+    // leave the earlier (simpler) candidate only for a clear win
+    if (best_ms < 0 || ms < best_ms * 0.97f) {
+      best_ms = ms;
+      out->patch = false;
+      out->tc = trial;
+      ok = true;
+    }
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (failed || !ok) return fail(perr.empty() ? "no launch candidate" : perr);
+  return true;
+}
+
+// The flat launch list of one forward pass at `batch` clips.  Optionally (RNB_B200_CHUNK_MB > 0) a
+// SpatioTemporalConv whose intermediate tensor (spatial output = temporal input, slot M) does not
+// survive in L2 is run in batch chunks -- spatial(chunk), temporal(chunk), ... -- so that the
+// intermediate is produced and consumed while cache resident, reusing the first chunk-sized part
+// of slot M.  ncu shows the unchunked conv2 temporal kernel re-reading all 115 MB from DRAM
+// (profiles/r01_ncu_conv_kernels_v2.md), but measured on B200 at B=16 the chunked schedule is
+// SLOWER (15.7k vs 16.8k clips/s at 32 MB chunks, 12.9k at 16 MB): every extra launch reloads the
+// resident weights and runs a short, badly quantised grid.  Hence off by default.
+bool R2P1DModel::build_plan(int batch, cudaStream_t stream, std::vector<Launch>* plan,
+                            std::string* err) {
+  static const double chunk_mb = [] {
+    const char* e = getenv("RNB_B200_CHUNK_MB");
+    return e ? atof(e) : 0.0;
+  }();
+  const int n = (int)ops_.size();
+  for (int i = 0; i < n; ++i) {
+    const ConvOp& op = ops_[i];
+    const bool pair = i + 1 < n && op.out_slot == SLOT_M && ops_[i + 1].in_slot == SLOT_M;
+    const double mid_mb_per_clip = (double)op.g.out_elems(1) * 2 / 1e6;
+    int bc = chunk_mb > 0 ? (int)(chunk_mb / mid_mb_per_clip) : batch;
+    if (bc < 1) bc = 1;
+    if (!pair || mid_mb_per_clip * batch <= 1.5 * chunk_mb || bc >= batch) {
+      Launch l;
+      if (!plan_conv(i, 0, batch, false, stream, nullptr, &l, err)) return false;
+      plan->push_back(l);
+      continue;
+    }
+    // chunked pair: tune once per distinct chunk size, copy the choice to the other chunks
+    std::map<int, std::pair<Launch, Launch>> tuned;
+    for (int first = 0; first < batch; first += bc) {
+      const int b = batch - first < bc ? batch - first : bc;
+      auto it = tuned.find(b);
+      Launch sp, tp;
+      if (!plan_conv(i, first, b, true, stream, it == tuned.end() ? nullptr : &it->second.first,
+                     &sp, err) ||
+          !plan_conv(i + 1, first, b, true, stream,
+                     it == tuned.end() ? nullptr : &it->second.second, &tp, err))
+        return false;
+      if (it == tuned.end()) tuned.emplace(b, std::make_pair(sp, tp));
+      plan->push_back(sp);
+      plan->push_back(tp);
+    }
+    ++i;  // the temporal half is planned
+  }
+  return true;
+}
+
+const std::vector<R2P1DModel::Launch>* R2P1DModel::ensure_plan(int batch, cudaStream_t stream,
+                                                               std::string* err) {
+  auto it = plans_.find(batch);
+  if (it == plans_.end()) {
+    std::vector<Launch> plan;
+    if (!build_plan(batch, stream, &plan, err)) return nullptr;
+    it = plans_.emplace(batch, std::move(plan)).first;
+  }
+  return &it->second;
 }
 
 int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int out_fmt,
@@ -416,105 +589,12 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
     if (err) *err = "unsupported output format " + std::to_string(out_fmt) + " for this handle";
     return RNB_EINVAL;
   }
-  // ---- launch plans for this batch size (first use only).  Built BEFORE the input is staged:
+  // ---- launch plan for this batch size (first use only).  Built BEFORE the input is staged:
   // tuning launches the convolutions on whatever the arena holds and overwrites every slot.
+  const std::vector<Launch>* plan = nullptr;
   if (tc) {
-    auto it = plans_.find(batch);
-    if (it == plans_.end()) {
-      std::vector<OpPlan> plan(ops_.size());
-      for (size_t i = 0; i < ops_.size(); ++i) {
-        const ConvOp& op = ops_[i];
-        std::string perr;
-        const __nv_bfloat16* x = (const __nv_bfloat16*)slots_[op.in_slot];
-        const __nv_bfloat16* w = (const __nv_bfloat16*)op.d_w;
-        __nv_bfloat16* y = (__nv_bfloat16*)slots_[op.out_slot];
-        const __nv_bfloat16* res =
-            op.res_slot >= 0 ? (const __nv_bfloat16*)slots_[op.res_slot] : nullptr;
-        // Candidates: the patch kernel (always taken when its weights are resident), and the tap
-        // kernel in each cluster shape.  Which is fastest depends on the layer (shared-memory
-        // bandwidth vs. tile fit vs. lock-step between CTAs), so time them once per (layer, batch
-        // size) -- the reference runs with cudnn.benchmark = True for the same reason
-        // (runner.py:25).
-        // RNB_B200_PATCH_STREAM=0 keeps streamed-weight patch launches out of the candidate set
-        static const bool allow_stream = [] {
-          const char* e = getenv("RNB_B200_PATCH_STREAM");
-          return !(e && e[0] == '0');
-        }();
-        const bool patch_ok =
-            conv_patch_applicable(op.g) && (allow_stream || !conv_patch_streams(op.g));
-        const bool patch_only = patch_ok && !conv_patch_streams(op.g);
-        bool ok = false;
-        float best_ms = -1.f;
-        cudaEvent_t e0, e1;
-        if (!cuda_ok(cudaEventCreate(&e0), "cudaEventCreate", err) ||
-            !cuda_ok(cudaEventCreate(&e1), "cudaEventCreate", err))
-          return RNB_ECUDA;
-        auto time_it = [&](auto&& launch, float* ms) -> bool {
-          cudaError_t te = launch();
-          if (te == cudaSuccess) te = cudaEventRecord(e0, stream);
-          for (int r = 0; r < 8 && te == cudaSuccess; ++r) te = launch();
-          if (te == cudaSuccess) te = cudaEventRecord(e1, stream);
-          if (te == cudaSuccess) te = cudaEventSynchronize(e1);
-          if (te == cudaSuccess) te = cudaEventElapsedTime(ms, e0, e1);
-          if (te != cudaSuccess) perr = std::string("plan timing: ") + cudaGetErrorString(te);
-          return te == cudaSuccess;
-        };
-        bool failed = false;
-        if (patch_ok) {
-          ConvPatchParams trial;
-          if (!build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &trial,
-                                       &perr)) {
-            failed = true;
-          } else if (patch_only) {
-            plan[i].patch = true;
-            plan[i].pp = trial;
-            ok = true;
-          } else {
-            float ms = 0.f;
-            if (!time_it([&] { return launch_conv_patch(trial, num_sms_, stream); }, &ms)) {
-              failed = true;
-            } else {
-              best_ms = ms;
-              plan[i].patch = true;
-              plan[i].pp = trial;
-              ok = true;
-            }
-          }
-        }
-        if (!patch_only && !failed) {
-          static const int cand[6][2] = {{1, 1}, {2, 1}, {4, 1}, {1, 2}, {2, 2}, {1, 4}};
-          for (const auto& c : cand) {
-            ConvTcParams trial;
-            if (!build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_,
-                                      &trial, &perr, c[0], c[1])) {
-              failed = true;
-              break;
-            }
-            if (trial.cm != c[0] || trial.cn != c[1]) continue;  // shape not applicable here
-            float ms = 0.f;
-            if (!time_it([&] { return launch_conv_tc(trial, num_sms_, stream); }, &ms)) {
-              failed = true;
-              break;
-            }
-            // leave the earlier (simpler) candidate only for a clear win
-            if (best_ms < 0 || ms < best_ms * 0.97f) {
-              best_ms = ms;
-              plan[i].patch = false;
-              plan[i].tc = trial;
-              ok = true;
-            }
-          }
-        }
-        cudaEventDestroy(e0);
-        cudaEventDestroy(e1);
-        if (failed) ok = false;
-        if (!ok) {
-          if (err) *err = op.name + ": " + perr;
-          return RNB_ECUDA;
-        }
-      }
-      it = plans_.emplace(batch, std::move(plan)).first;
-    }
+    plan = ensure_plan(batch, stream, err);
+    if (!plan) return RNB_ECUDA;
   }
   cudaError_t e = cudaSuccess;
   mark();
@@ -556,12 +636,10 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
 
   // ---- convolutions
   if (tc) {
-    auto it = plans_.find(batch);
-    for (size_t i = 0; i < ops_.size(); ++i) {
-      const OpPlan& op = it->second[i];
-      const cudaError_t le = op.patch ? launch_conv_patch(op.pp, num_sms_, stream)
-                                      : launch_conv_tc(op.tc, num_sms_, stream);
-      if (!cuda_ok(le, ops_[i].name.c_str(), err)) return RNB_ECUDA;
+    for (const Launch& l : *plan) {
+      const cudaError_t le = l.patch ? launch_conv_patch(l.pp, num_sms_, stream)
+                                     : launch_conv_tc(l.tc, num_sms_, stream);
+      if (!cuda_ok(le, ops_[l.op].name.c_str(), err)) return RNB_ECUDA;
       mark();
     }
   } else {
@@ -614,6 +692,7 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
   }
   if (!cuda_ok(e, "output stage", err)) return RNB_ECUDA;
   mark();
+  last_launches_ = (tc ? (int)plan->size() : (int)ops_.size()) + 2;
   return RNB_OK;
 }
 

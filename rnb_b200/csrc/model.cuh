@@ -40,7 +40,7 @@ class R2P1DModel {
   bool load_param(const char* key, const float* data, const int64_t* shape, int ndim,
                   std::string* err);
   int finalize(std::string* err);  // RNB_* code
-  // `events`, when given, receives num_launches()+1 events recorded around every kernel
+  // `events`, when given, receives one event before the first kernel and one after every kernel
   int forward(const void* in, int in_fmt, int batch, void* out, int out_fmt, cudaStream_t stream,
               std::string* err, cudaEvent_t* events = nullptr, float* video_sum = nullptr,
               int* video_cls = nullptr, bool video = false);
@@ -50,7 +50,9 @@ class R2P1DModel {
                double* weight_bytes, int* kernel_kind) const;
   void io_shape(int which, int64_t shape4[4]) const;
   double flops(int batch) const;
-  int num_launches() const { return (int)ops_.size() + 2; }
+  // kernels the most recent forward launched (convolutions + staging + classifier/layout)
+  int num_launches() const { return last_launches_ > 0 ? last_launches_ : (int)ops_.size() + 2; }
+  int num_ops() const { return (int)ops_.size(); }
   bool finalized() const { return finalized_; }
 
  private:
@@ -82,14 +84,21 @@ class R2P1DModel {
   void* d_classify_scratch_ = nullptr;  // staged logits + arrival counter of the fused classifier
   float* d_fc_w_ = nullptr;
   float* d_fc_b_ = nullptr;
-  // tensor-core launch plan of one convolution for one batch size: the patch kernel where it
-  // applies (stride-1 3x3 / 3x1x1 layers whose weights fit in shared memory), else the tap kernel
-  struct OpPlan {
+  // One kernel launch of the tensor-core plan: convolution `op` over `batch` clips starting at clip
+  // `first`, through the patch kernel where it applies, else the tap kernel.
+  struct Launch {
+    int op = 0;
+    int first = 0, batch = 0;
     bool patch = false;
     ConvTcParams tc;
     ConvPatchParams pp;
   };
-  std::map<int, std::vector<OpPlan>> plans_;
+  bool plan_conv(int op_index, int first, int batch, bool chunked, cudaStream_t stream,
+                 const Launch* like, Launch* out, std::string* err);
+  bool build_plan(int batch, cudaStream_t stream, std::vector<Launch>* plan, std::string* err);
+  const std::vector<Launch>* ensure_plan(int batch, cudaStream_t stream, std::string* err);
+  std::map<int, std::vector<Launch>> plans_;  // per batch size
+  int last_launches_ = 0;                     // kernels launched by the most recent forward
 };
 
 }  // namespace rnb

@@ -173,13 +173,18 @@ class R2P1DEngine:
 
     @property
     def num_launches(self):
+        """Kernels the most recent forward launched."""
         return int(self.lib.rnb_r2p1d_num_launches(self._handle))
+
+    @property
+    def num_convs(self):
+        return int(self.lib.rnb_r2p1d_num_convs(self._handle))
 
     def op_info(self):
         """[(state_dict prefix, FLOPs per clip, activation bytes per clip, weight bytes, kernel)]
         per convolution; kernel is 'conv_ref', 'conv_tc' or 'conv_patch'."""
         info = []
-        for i in range(self.num_launches - 2):
+        for i in range(self.num_convs):
             name = ctypes.create_string_buffer(256)
             f, a, w, k = ctypes.c_double(), ctypes.c_double(), ctypes.c_double(), ctypes.c_int()
             _lib.check(self.lib.rnb_r2p1d_op_info(self._handle, i, name, 256, ctypes.byref(f),
@@ -194,7 +199,7 @@ class R2P1DEngine:
         x, fmt, batch = self._check_input(x)
         out = self._out[:batch]
         out_fmt = _lib.FMT_F32_LOGITS if self.end_index == 5 else _lib.FMT_F32_NCDHW
-        n = self.num_launches
+        n = self.num_convs + 2
         ms = (ctypes.c_float * n)()
         stream = torch.cuda.current_stream(self.device).cuda_stream
         _lib.check(self.lib.rnb_r2p1d_profile(self._handle, ctypes.c_void_p(x.data_ptr()), fmt,

@@ -156,7 +156,11 @@ def test_r34_runner_form_layer_sizes(lib, golden):
 def test_flops_and_launch_count(engines):
     eng = engines('bf16', False)
     assert abs(eng.flops(1) / 1e9 - 42.172) < 0.01
+    assert eng.num_convs == 40
+    eng(R.synthetic_clips(2, seed=1).to(DEV))
     assert eng.num_launches == 42  # 40 convolutions + input staging + pool/classifier
+    ms = eng.profile(R.synthetic_clips(16, seed=1).to(DEV))
+    assert len(ms) == 42 and all(t > 0 for t in ms)
 
 
 def test_batch_gather_bit_exact(lib):
@@ -371,3 +375,30 @@ def test_host_pipeline_end_to_end(engines, models):
     for hb, got in zip(batches, outs):
         want = R.forward_u8(models[True], hb)
         check_logits(got, want, 'bf16')
+
+
+def test_chunked_schedule_gives_identical_logits(lib, tmp_path):
+    """RNB_B200_CHUNK_MB > 0 runs each spatial->temporal pair in batch chunks through one reused
+    intermediate buffer; a scheduling change only, so the logits must be bit-identical."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, torch; sys.path.insert(0, %r)\n"
+        "from rnb_b200.engine import R2P1DEngine, random_state_dict\n"
+        "sd = random_state_dict(seed=3)\n"
+        "eng = R2P1DEngine('cuda:0', sd, max_batch=16)\n"
+        "g = torch.Generator().manual_seed(9)\n"
+        "x = torch.randint(0, 256, (16, 8, 3, 112, 112), dtype=torch.uint8, generator=g).cuda()\n"
+        "y = eng(x).cpu(); torch.cuda.synchronize()\n"
+        "torch.save((y, eng.num_launches), sys.argv[1])\n" % root)
+    outs = []
+    for chunk in ('0', '20'):
+        path = str(tmp_path / ('logits_%s.pt' % chunk))
+        env = dict(os.environ, RNB_B200_CHUNK_MB=chunk)
+        subprocess.run([sys.executable, '-c', code, path], check=True, env=env, timeout=600)
+        outs.append(torch.load(path))
+    (y0, n0), (y1, n1) = outs
+    assert n0 == 42 and n1 > 42
+    assert torch.equal(y0, y1)
