@@ -25,11 +25,14 @@ struct PatchItem {
   int n0, ncols;      // channel tile
 };
 
-// work items: channel tile fastest, then the position tiles in (w, h, t, b) order
-__device__ __forceinline__ PatchItem decode_patch_item(const ConvPatchParams& p, int item) {
+// work items: channel tile fastest, then the position tiles in (w, h, t, b) order.  In pair mode an
+// item covers two consecutive position tiles, one per CTA of the pair (`rank`); the second may lie
+// past the last tile, its batch index is then out of range and everything it touches is masked.
+__device__ __forceinline__ PatchItem decode_patch_item(const ConvPatchParams& p, int item, int pair,
+                                                       int rank) {
   PatchItem c;
   const int nt = item % p.n_tiles;
-  int tile = item / p.n_tiles;
+  int tile = (item / p.n_tiles) * pair + rank;
   const int iw = tile % p.tiles_w;
   tile /= p.tiles_w;
   const int ih = tile % p.tiles_h;
@@ -46,7 +49,13 @@ __device__ __forceinline__ PatchItem decode_patch_item(const ConvPatchParams& p,
 
 }  // namespace
 
-template <bool kRes, bool kRelu, bool kStream>
+// kPair: two CTAs of a cluster issue ONE tcgen05.mma.cta_group::2 (M = 256): each CTA holds its own
+// position tile (patch, accumulator, epilogue) and HALF of every weight tile.  That halves the
+// weight-side shared-memory reads and fills, which is what caps the single-CTA kernel (UMMA operand
+// reads 64*(M+N)/N B/clk plus TMA fills against a 128 B/clk port).  The leader (rank 0) issues all
+// MMAs; both CTAs' TMA loads signal the leader's "full" barriers, the leader's commits release the
+// buffers and publish the accumulators in both CTAs.
+template <bool kRes, bool kRelu, bool kStream, bool kPair>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -55,36 +64,55 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
-  const uint32_t wtile_bytes = p.block_n * 128;         // one (tap, channel block) weight tile
+  // (shuffle-broadcast like `warp`: the MMA role branches on it and must stay provably uniform)
+  // rank inside the 2-CTA cluster; for a (2,1,1) cluster over a 1-D grid that is blockIdx.x & 1,
+  // which -- unlike a read of %cluster_ctarank -- the compiler can prove uniform
+  const uint32_t rank = kPair ? (blockIdx.x & 1u) : 0u;
+  constexpr int kNumCta = kPair ? 2 : 1;
+  // one (tap, channel block) weight tile, or this CTA's half of it
+  const uint32_t wtile_bytes = (p.block_n / kNumCta) * 128;
   const uint32_t n_wtiles = p.num_taps * p.nkb;
   const uint32_t n_wslots = kStream ? (uint32_t)p.b_stages : n_wtiles;
   const uint32_t pblock_bytes = p.patch_rows * 128;     // one channel block of a patch
   const uint32_t patch_bytes = p.nkb * pblock_bytes;
   const uint32_t wbuf = smem_base;
   const uint32_t pbuf = wbuf + n_wslots * wtile_bytes;
-  const uint32_t bars = pbuf + 2 * patch_bytes + 1024;  // +1024: rows past the last patch that
-                                                        // only garbage accumulator rows read
+  const uint32_t bars = pbuf + p.p_bufs * patch_bytes + 1024;  // +1024: rows past the last patch
+                                                               // that only garbage rows read
   const uint32_t w_full = bars;
-  const uint32_t p_full = bars + 8;    // [2]
-  const uint32_t p_empty = bars + 24;  // [2]
-  const uint32_t tmem_full_bar = bars + 40;   // [2]
-  const uint32_t tmem_empty_bar = bars + 56;  // [2]
-  const uint32_t tmem_ptr_smem = bars + 72;
-  const uint32_t b_full = bars + 80;                          // [kPatchMaxBStages]
-  const uint32_t b_empty = bars + 80 + 8 * kPatchMaxBStages;  // [kPatchMaxBStages]
+  const uint32_t p_full = bars + 8;                     // [kPatchMaxBufs]
+  const uint32_t p_empty = p_full + 8 * kPatchMaxBufs;  // [kPatchMaxBufs]
+  const uint32_t tmem_full_bar = p_empty + 8 * kPatchMaxBufs;  // [2]
+  const uint32_t tmem_empty_bar = tmem_full_bar + 16;          // [2]
+  const uint32_t tmem_ptr_smem = tmem_empty_bar + 16;
+  const uint32_t b_full = tmem_ptr_smem + 8;                  // [kPatchMaxBStages]
+  const uint32_t b_empty = b_full + 8 * kPatchMaxBStages;     // [kPatchMaxBStages]
+  static_assert(8 + 16 * kPatchMaxBufs + 32 + 8 + 16 * kPatchMaxBStages <= 256, "barrier area");
   const uint32_t shift_tab = bars + 256;
 
-  const int total_items = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b * p.n_tiles;
+  const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b;
+  const int total_items = ((total_tiles + kNumCta - 1) / kNumCta) * p.n_tiles;
+  const int first_item = blockIdx.x / kNumCta;
+  const int item_step = gridDim.x / kNumCta;
+  // barriers the MMA warp waits on live in the leader; both CTAs' loads signal them
+  const uint32_t w_full_ld = kPair ? ptx::map_to_cta(w_full, 0) : w_full;
+  const uint32_t p_full_ld = kPair ? ptx::map_to_cta(p_full, 0) : p_full;
+  const uint32_t b_full_ld = kPair ? ptx::map_to_cta(b_full, 0) : b_full;
+  const uint32_t tmem_empty_ld = kPair ? ptx::map_to_cta(tmem_empty_bar, 0) : tmem_empty_bar;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.a_map);
     ptx::prefetch_tmap(&p.b_map);
     ptx::mbar_init(w_full, 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < kPatchMaxBufs; ++s) {
       ptx::mbar_init(p_full + 8 * s, 1);
       ptx::mbar_init(p_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(tmem_full_bar + 8 * s, 1);
-      ptx::mbar_init(tmem_empty_bar + 8 * s, kEpiThreads);
+      // pair mode: one arrival per CTA (its epilogue warps meet on a named barrier first) --
+      // hundreds of remote arrivals per tile on one mbarrier serialise
+      ptx::mbar_init(tmem_empty_bar + 8 * s, kPair ? 2 : kEpiThreads);
     }
     for (int s = 0; s < kPatchMaxBStages; ++s) {
       ptx::mbar_init(b_full + 8 * s, 1);
@@ -93,8 +121,13 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     ptx::fence_mbar_init();
   }
   if (warp == 1) {
-    ptx::tmem_alloc(tmem_ptr_smem, kTmemCols);
-    ptx::tmem_relinquish();
+    if (kPair) {
+      ptx::tmem_alloc_pair(tmem_ptr_smem, kTmemCols);
+      ptx::tmem_relinquish_pair();
+    } else {
+      ptx::tmem_alloc(tmem_ptr_smem, kTmemCols);
+      ptx::tmem_relinquish();
+    }
   }
   if (!kStream && threadIdx.x >= 64) {
     // one channel tile for the whole kernel: its shift table is loaded once
@@ -106,6 +139,9 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   }
   ptx::tc_fence_before();
   __syncthreads();
+  // the peer signals the leader's barriers and the leader's commits arrive on the peer's: nobody
+  // starts before both CTAs have initialised theirs
+  if (kPair) ptx::cluster_sync_all();
   ptx::tc_fence_after();
   ptx::grid_dep_launch_dependents();
   uint32_t tmem_base;
@@ -116,87 +152,135 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     // ------------------------------------------------------------------ TMA producer (warp-wide)
     if (!kStream) {
       // the packed weights are constants of the model: fetch them while the previous kernel in
-      // the stream is still draining, and only then wait for its activations
-      ptx::mbar_expect_tx_elect(w_full, n_wtiles * wtile_bytes);
+      // the stream is still draining, and only then wait for its activations.  In pair mode the
+      // leader announces the bytes of BOTH halves; each CTA fetches its own rows.
+      if (rank == 0) ptx::mbar_expect_tx_elect(w_full, kNumCta * n_wtiles * wtile_bytes);
+      const int row0 = rank * (p.n / kNumCta);
       for (int tap = 0, i = 0; tap < p.num_taps; ++tap)
-        for (int kb = 0; kb < p.nkb; ++kb, ++i)
-          ptx::tma_load_2d_elect(wbuf + i * wtile_bytes, &p.b_map, w_full,
-                                 tap * p.cin_pad + kb * 64, 0);
+        for (int kb = 0; kb < p.nkb; ++kb, ++i) {
+          if (kPair)
+            ptx::tma_load_2d_pair_elect(wbuf + i * wtile_bytes, &p.b_map, w_full_ld,
+                                        tap * p.cin_pad + kb * 64, row0);
+          else
+            ptx::tma_load_2d_elect(wbuf + i * wtile_bytes, &p.b_map, w_full,
+                                   tap * p.cin_pad + kb * 64, 0);
+        }
     }
     ptx::grid_dep_wait();
-    int local = 0;
+    uint32_t pb = 0, ph = 0;
     uint32_t bs = 0, bphase = 0;
-    for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++local) {
-      const PatchItem tc = decode_patch_item(p, item);
-      const uint32_t pb = local & 1;
-      const uint32_t ph = (local >> 1) & 1;
+    for (int item = first_item; item < total_items; item += item_step) {
+      const PatchItem tc = decode_patch_item(p, item, kNumCta, rank);
       ptx::mbar_wait(p_empty + 8 * pb, ph ^ 1);
-      ptx::mbar_expect_tx_elect(p_full + 8 * pb, patch_bytes);
-      for (int kb = 0; kb < p.nkb; ++kb)
-        ptx::tma_load_5d_elect(pbuf + pb * patch_bytes + kb * pblock_bytes, &p.a_map,
-                               p_full + 8 * pb, kb * 64, tc.w0 + p.aw, tc.h0 + p.ah, tc.t0 + p.at,
-                               tc.b);
+      if (rank == 0) ptx::mbar_expect_tx_elect(p_full + 8 * pb, kNumCta * patch_bytes);
+      for (int kb = 0; kb < p.nkb; ++kb) {
+        const uint32_t dst = pbuf + pb * patch_bytes + kb * pblock_bytes;
+        if (kPair)
+          ptx::tma_load_5d_pair_elect(dst, &p.a_map, p_full_ld + 8 * pb, kb * 64, tc.w0 + p.aw,
+                                      tc.h0 + p.ah, tc.t0 + p.at, tc.b);
+        else
+          ptx::tma_load_5d_elect(dst, &p.a_map, p_full + 8 * pb, kb * 64, tc.w0 + p.aw,
+                                 tc.h0 + p.ah, tc.t0 + p.at, tc.b);
+      }
       if (kStream) {
+        // my rows of the channel tile: the MMA takes columns [0, N/2) from the leader's shared
+        // memory and [N/2, N) from the peer's
+        const int brow = tc.n0 + rank * (tc.ncols / kNumCta);
         for (int tap = 0; tap < p.num_taps; ++tap)
           for (int kb = 0; kb < p.nkb; ++kb) {
             ptx::mbar_wait(b_empty + 8 * bs, bphase ^ 1);
-            ptx::mbar_expect_tx_elect(b_full + 8 * bs, wtile_bytes);
-            ptx::tma_load_2d_elect(wbuf + bs * wtile_bytes, &p.b_map, b_full + 8 * bs,
-                                   tap * p.cin_pad + kb * 64, tc.n0);
+            if (rank == 0) ptx::mbar_expect_tx_elect(b_full + 8 * bs, kNumCta * wtile_bytes);
+            if (kPair)
+              ptx::tma_load_2d_pair_elect(wbuf + bs * wtile_bytes, &p.b_map, b_full_ld + 8 * bs,
+                                          tap * p.cin_pad + kb * 64, brow);
+            else
+              ptx::tma_load_2d_elect(wbuf + bs * wtile_bytes, &p.b_map, b_full + 8 * bs,
+                                     tap * p.cin_pad + kb * 64, brow);
             if (++bs == (uint32_t)p.b_stages) {
               bs = 0;
               bphase ^= 1;
             }
           }
+      }
+      if (++pb == (uint32_t)p.p_bufs) {
+        pb = 0;
+        ph ^= 1;
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (warp-wide)
     // (reads only shared memory and TMEM: ordered behind the producer's grid_dep_wait by the
-    // patch-full barrier)
-    if (!kStream) ptx::mbar_wait(w_full, 0);
-    int local = 0;
-    uint32_t bs = 0, bphase = 0;
-    for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++local) {
-      const PatchItem tc = decode_patch_item(p, item);
-      const uint32_t idesc = ptx::make_idesc_bf16_m128((uint32_t)tc.ncols);
-      const uint32_t pb = local & 1;
-      const uint32_t ph = (local >> 1) & 1;
-      const uint32_t tmem_d = tmem_base + pb * kMaxBlockN;
-      ptx::mbar_wait(tmem_empty_bar + 8 * pb, ph ^ 1);
-      ptx::mbar_wait(p_full + 8 * pb, ph);
-      ptx::tc_fence_after();
-      uint32_t accumulate = 0;
-      uint32_t wt = wbuf;
-      for (int tap = 0; tap < p.num_taps; ++tap) {
-        const uint32_t arow = pbuf + pb * patch_bytes + (uint32_t)p.tap_shift[tap] * 128u;
-        for (int kb = 0; kb < p.nkb; ++kb) {
-          if (kStream) {
-            ptx::mbar_wait(b_full + 8 * bs, bphase);
-            ptx::tc_fence_after();
-            wt = wbuf + bs * wtile_bytes;
-          }
-          const uint64_t adesc = ptx::make_kmajor_desc(arow + kb * pblock_bytes, 128);
-          const uint64_t bdesc = ptx::make_kmajor_desc(wt, 128);
-          const int ksteps = min(64, p.cin_pad - kb * 64) >> 4;
-          ptx::umma_bf16_elect(tmem_d, adesc, bdesc, idesc, accumulate);
-          if (ksteps > 1) ptx::umma_bf16_elect(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
-          if (ksteps > 2) ptx::umma_bf16_elect(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
-          if (ksteps > 3) ptx::umma_bf16_elect(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
-          accumulate = 1;
-          if (kStream) {
-            ptx::umma_commit_elect(b_empty + 8 * bs);
-            if (++bs == (uint32_t)p.b_stages) {
-              bs = 0;
-              bphase ^= 1;
+    // patch-full barrier).  In pair mode only the leader issues.
+    if (!kPair || rank == 0) {
+      if (!kStream) ptx::mbar_wait(w_full, 0);
+      int local = 0;
+      uint32_t pb = 0, ph = 0;
+      uint32_t bs = 0, bphase = 0;
+      // (Waiting for the NEXT tile's accumulator and patch half-way through the current tile, to
+      // take the ~450-cycle barrier round trip off the tile boundary, was measured slower: the
+      // previous tile's epilogue is not done by then and the MMA queue drains while the issuing
+      // thread blocks.  profiles/r01_mma_issue_notes.md)
+      for (int item = first_item; item < total_items; item += item_step, ++local) {
+        const PatchItem tc = decode_patch_item(p, item, kNumCta, 0);
+        const uint32_t idesc = kPair ? ptx::make_idesc_bf16_m256((uint32_t)tc.ncols)
+                                     : ptx::make_idesc_bf16_m128((uint32_t)tc.ncols);
+        const uint32_t acc = local & 1;
+        const uint32_t acc_phase = (local >> 1) & 1;
+        const uint32_t tmem_d = tmem_base + acc * kMaxBlockN;
+        ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1);
+        ptx::mbar_wait(p_full + 8 * pb, ph);
+        ptx::tc_fence_after();
+        uint32_t accumulate = 0;
+        uint32_t wt = wbuf;
+        for (int tap = 0; tap < p.num_taps; ++tap) {
+          const uint32_t arow = pbuf + pb * patch_bytes + (uint32_t)p.tap_shift[tap] * 128u;
+          for (int kb = 0; kb < p.nkb; ++kb) {
+            if (kStream) {
+              ptx::mbar_wait(b_full + 8 * bs, bphase);
+              ptx::tc_fence_after();
+              wt = wbuf + bs * wtile_bytes;
             }
-          } else {
-            wt += wtile_bytes;
+            const uint64_t adesc = ptx::make_kmajor_desc(arow + kb * pblock_bytes, 128);
+            const uint64_t bdesc = ptx::make_kmajor_desc(wt, 128);
+            const int ksteps = min(64, p.cin_pad - kb * 64) >> 4;
+            if (kPair) {
+              ptx::umma_bf16_pair_elect(tmem_d, adesc, bdesc, idesc, accumulate);
+              if (ksteps > 1) ptx::umma_bf16_pair_elect(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
+              if (ksteps > 2) ptx::umma_bf16_pair_elect(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
+              if (ksteps > 3) ptx::umma_bf16_pair_elect(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
+            } else {
+              ptx::umma_bf16_elect(tmem_d, adesc, bdesc, idesc, accumulate);
+              if (ksteps > 1) ptx::umma_bf16_elect(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
+              if (ksteps > 2) ptx::umma_bf16_elect(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
+              if (ksteps > 3) ptx::umma_bf16_elect(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
+            }
+            accumulate = 1;
+            if (kStream) {
+              if (kPair)
+                ptx::umma_commit_pair_elect(b_empty + 8 * bs, 3);
+              else
+                ptx::umma_commit_elect(b_empty + 8 * bs);
+              if (++bs == (uint32_t)p.b_stages) {
+                bs = 0;
+                bphase ^= 1;
+              }
+            } else {
+              wt += wtile_bytes;
+            }
           }
         }
+        if (kPair) {
+          ptx::umma_commit_pair_elect(p_empty + 8 * pb, 3);
+          ptx::umma_commit_pair_elect(tmem_full_bar + 8 * acc, 3);
+        } else {
+          ptx::umma_commit_elect(p_empty + 8 * pb);
+          ptx::umma_commit_elect(tmem_full_bar + 8 * acc);
+        }
+        if (++pb == (uint32_t)p.p_bufs) {
+          pb = 0;
+          ph ^= 1;
+        }
       }
-      ptx::umma_commit_elect(p_empty + 8 * pb);
-      ptx::umma_commit_elect(tmem_full_bar + 8 * pb);
     }
   } else {
     // ------------------------------------------------------------------ epilogue (256 threads)
@@ -212,12 +296,12 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     const bool in_tile = (rw < p.tw) && (rh < p.th) && (rt < p.tt);
     int local = 0;
     int table_n0 = kStream ? -1 : 0;
-    for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++local) {
-      const PatchItem tc = decode_patch_item(p, item);
+    for (int item = first_item; item < total_items; item += item_step, ++local) {
+      const PatchItem tc = decode_patch_item(p, item, kNumCta, rank);
       const uint32_t acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
       const int w = tc.w0 + rw, h = tc.h0 + rh, t = tc.t0 + rt;
-      const bool valid = in_tile && (w < p.Wo) && (h < p.Ho) && (t < p.To);
+      const bool valid = in_tile && (w < p.Wo) && (h < p.Ho) && (t < p.To) && (tc.b < p.B);
       const size_t off =
           ((((size_t)tc.b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad + tc.n0;
       __nv_bfloat16* out_row = p.y + off;
@@ -267,61 +351,100 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
         if (valid) ptx::st_global_v8(out_row + col, o);
       }
       ptx::tc_fence_before();
-      ptx::mbar_arrive(tmem_empty_bar + 8 * acc);
+      if (kPair) {
+        ptx::named_bar_sync(2, kEpiThreads);
+        if (et == 0) ptx::mbar_arrive_cluster(tmem_empty_ld + 8 * acc);
+      } else {
+        ptx::mbar_arrive(tmem_empty_bar + 8 * acc);
+      }
     }
   }
 
   ptx::tc_fence_before();
   __syncthreads();
+  // the leader's last commits may still be on their way to the peer's barriers
+  if (kPair) ptx::cluster_sync_all();
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, kTmemCols);
+    if (kPair)
+      ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
+    else
+      ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
 namespace {
-template <bool kRes, bool kRelu, bool kStream>
-cudaError_t launch_patch_variant(const ConvPatchParams& p, int grid, int smem, cudaStream_t stream) {
+template <bool kRes, bool kRelu, bool kStream, bool kPair>
+cudaError_t launch_patch_variant(const ConvPatchParams& p, int num_sms, int smem,
+                                 cudaStream_t stream) {
   static bool configured[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   if (dev >= 0 && dev < 64 && !configured[dev]) {
-    e = cudaFuncSetAttribute(conv_patch_kernel<kRes, kRelu, kStream>,
+    e = cudaFuncSetAttribute(conv_patch_kernel<kRes, kRelu, kStream, kPair>,
                              cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (e != cudaSuccess) return e;
     configured[dev] = true;
   }
+  const int ncta = kPair ? 2 : 1;
+  const int tiles = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b;
+  const int items = ((tiles + ncta - 1) / ncta) * p.n_tiles;
+  int max_groups = num_sms / ncta;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, conv_patch_kernel<kRes, kRelu, kStream>, p);
+  if (kPair) {
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = 2;
+    attr[1].val.clusterDim.y = 1;
+    attr[1].val.clusterDim.z = 1;
+    cfg.numAttrs = 2;
+    // A persistent grid must be fully resident.  Not every SM has a partner for a 2-CTA cluster
+    // (SMs fused off leave single-SM TPCs), so ask how many pairs fit at once.
+    static int cached[64] = {};
+    if (dev >= 0 && dev < 64 && cached[dev] == 0) {
+      cfg.gridDim = dim3(2 * (num_sms / 2));
+      int n = 0;
+      e = cudaOccupancyMaxActiveClusters(&n, conv_patch_kernel<kRes, kRelu, kStream, kPair>, &cfg);
+      if (e != cudaSuccess) return e;
+      cached[dev] = n > 0 ? n : 1;
+    }
+    if (dev >= 0 && dev < 64 && cached[dev] < max_groups) max_groups = cached[dev];
+  }
+  const int groups = items < max_groups ? items : max_groups;
+  cfg.gridDim = dim3(groups * ncta);
+  return cudaLaunchKernelEx(&cfg, conv_patch_kernel<kRes, kRelu, kStream, kPair>, p);
 }
 
-template <bool kStream>
-cudaError_t launch_patch_mode(const ConvPatchParams& p, int grid, int smem, cudaStream_t stream) {
+template <bool kStream, bool kPair>
+cudaError_t launch_patch_mode(const ConvPatchParams& p, int num_sms, int smem, cudaStream_t stream) {
   const bool res = p.residual != nullptr, relu = p.relu != 0;
-  if (res) return relu ? launch_patch_variant<true, true, kStream>(p, grid, smem, stream)
-                       : launch_patch_variant<true, false, kStream>(p, grid, smem, stream);
-  return relu ? launch_patch_variant<false, true, kStream>(p, grid, smem, stream)
-              : launch_patch_variant<false, false, kStream>(p, grid, smem, stream);
+  if (res)
+    return relu ? launch_patch_variant<true, true, kStream, kPair>(p, num_sms, smem, stream)
+                : launch_patch_variant<true, false, kStream, kPair>(p, num_sms, smem, stream);
+  return relu ? launch_patch_variant<false, true, kStream, kPair>(p, num_sms, smem, stream)
+              : launch_patch_variant<false, false, kStream, kPair>(p, num_sms, smem, stream);
 }
 }  // namespace
 
 cudaError_t launch_conv_patch(const ConvPatchParams& p, int num_sms, cudaStream_t stream) {
   if (p.b_stages < 0 || p.b_stages > kPatchMaxBStages) return cudaErrorInvalidValue;
-  const int smem = conv_patch_smem_bytes(p.nkb, p.patch_rows, p.num_taps, p.block_n, p.b_stages);
-  const int total = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b * p.n_tiles;
-  const int grid = total < num_sms ? total : num_sms;
-  return p.b_stages > 0 ? launch_patch_mode<true>(p, grid, smem, stream)
-                        : launch_patch_mode<false>(p, grid, smem, stream);
+  const int ncta = p.pair ? 2 : 1;
+  if (p.p_bufs < 2 || p.p_bufs > kPatchMaxBufs) return cudaErrorInvalidValue;
+  const int smem = conv_patch_smem_bytes(p.nkb, p.patch_rows, p.num_taps, p.block_n / ncta,
+                                         p.b_stages, p.p_bufs);
+  if (p.pair)
+    return p.b_stages > 0 ? launch_patch_mode<true, true>(p, num_sms, smem, stream)
+                          : launch_patch_mode<false, true>(p, num_sms, smem, stream);
+  return p.b_stages > 0 ? launch_patch_mode<true, false>(p, num_sms, smem, stream)
+                        : launch_patch_mode<false, false>(p, num_sms, smem, stream);
 }
 
 }  // namespace rnb

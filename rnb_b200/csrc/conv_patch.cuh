@@ -24,6 +24,7 @@ namespace rnb {
 
 constexpr int kPatchMaxKb = 4;      // 64-channel blocks per patch
 constexpr int kPatchMaxBStages = 8;
+constexpr int kPatchMaxBufs = 4;    // activation patches in flight
 
 struct ConvPatchParams {
   alignas(64) CUtensorMap a_map;  // activation (C, W, H, T, B), box (64, pbox_w, pbox_h, pbox_t, 1)
@@ -38,6 +39,8 @@ struct ConvPatchParams {
   int n;                // output channels (multiple of 16)
   int n_tiles, block_n; // channel tiling: resident mode has one tile of n channels
   int b_stages;         // 0: weights resident; > 0: ring depth of the streamed weight tiles
+  int p_bufs;           // patch ring depth (2..kPatchMaxBufs)
+  int pair;             // 1: CTA pairs (cta_group::2), each CTA holds half of every weight tile
   // output tile: tw x th x tt positions, laid out in the accumulator with power-of-two pitches
   int tw, th, tt;
   int lpw, lph;         // log2 of the row pitches: row = (t << (lpw + lph)) + (h << lpw) + w
@@ -49,10 +52,12 @@ struct ConvPatchParams {
   int16_t tap_shift[kMaxTaps];  // row offset of each tap inside the patch
 };
 
-inline int conv_patch_smem_bytes(int nkb, int patch_rows, int num_taps, int block_n, int b_stages) {
+// block_n here is the rows of a weight tile that ONE CTA holds (half the channel tile in pair mode)
+inline int conv_patch_smem_bytes(int nkb, int patch_rows, int num_taps, int block_n, int b_stages,
+                                 int p_bufs = 2) {
   const int wtiles = b_stages > 0 ? b_stages : num_taps * nkb;
-  return 1024 + wtiles * block_n * 128 + 2 * nkb * patch_rows * 128 + 1024 /*slack rows*/ + 256 +
-         kMaxBlockN * 4;
+  return 1024 + wtiles * block_n * 128 + p_bufs * nkb * patch_rows * 128 + 1024 /*slack rows*/ +
+         256 + kMaxBlockN * 4;
 }
 
 cudaError_t launch_conv_patch(const ConvPatchParams& p, int num_sms, cudaStream_t stream);

@@ -80,7 +80,9 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
 
   // ---- cluster geometry
   const int csize = p.cm * p.cn;
-  const uint32_t crank = csize > 1 ? ptx::cluster_ctarank() : 0u;
+  // rank inside the (csize,1,1) cluster of a 1-D grid = blockIdx.x % csize, which -- unlike a read
+  // of %cluster_ctarank -- the compiler can prove warp-uniform (keeps the MMA issue loop short)
+  const uint32_t crank = csize > 1 ? (uint32_t)(blockIdx.x % csize) : 0u;
   ItemIter items;
   items.cm = p.cm;
   items.cn = p.cn;

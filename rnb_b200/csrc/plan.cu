@@ -349,7 +349,7 @@ struct PatchShape {
   int nkb = 0, patch_rows = 0, taps = 0;
   int tw = 0, th = 0, tt = 0, lpw = 0, lph = 0;
   int pbw = 0, pbh = 0, pbt = 0;  // patch box extent
-  int n_tiles = 1, block_n = 0, b_stages = 0;
+  int n_tiles = 1, block_n = 0, b_stages = 0, p_bufs = 2;
   double eff = 0;
 };
 
@@ -359,7 +359,8 @@ int ilog2(int v) {
   return l;
 }
 
-PatchShape patch_shape(const ConvGeom& g) {
+PatchShape patch_shape(const ConvGeom& g, int pair) {
+  const int ncta = pair ? 2 : 1;
   PatchShape s;
   if (g.stem_unfolded || g.st != 1 || g.sh != 1 || g.sw != 1) return s;
   s.nkb = ceil_div(g.cin_pad(), 64);
@@ -407,41 +408,50 @@ PatchShape patch_shape(const ConvGeom& g) {
   if (s.eff < 0.6) return s;
   s.patch_rows = s.pbw * s.pbh * s.pbt;
   // weights resident if they fit next to two patches, otherwise streamed per channel tile
-  if (np <= kMaxBlockN && conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np, 0) <= kSmemLimit) {
+  if (np <= kMaxBlockN &&
+      conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np / ncta, 0) <= kSmemLimit) {
     s.n_tiles = 1;
     s.block_n = np;
     s.b_stages = 0;
+    while (s.p_bufs < kPatchMaxBufs &&
+           conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np / ncta, 0, s.p_bufs + 1) <= kSmemLimit)
+      ++s.p_bufs;
     s.ok = true;
     return s;
   }
   for (int nt = ceil_div(np, kMaxBlockN); nt <= 8; ++nt) {
     const int bn = round_up(ceil_div(np, nt), 16);
-    const int fixed = conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, bn, 1) - bn * 128;
-    int stages = (kSmemLimit - fixed) / (bn * 128);
-    if (stages > kPatchMaxBStages) stages = kPatchMaxBStages;
-    if (stages >= 4 && bn >= 64) {
-      s.n_tiles = ceil_div(np, bn);
-      s.block_n = bn;
-      s.b_stages = stages;
-      s.ok = true;
-      return s;
+    const int stage = (bn / ncta) * 128;  // a CTA of a pair holds half of every weight tile
+    for (int pbufs = 3; pbufs >= 2; --pbufs) {
+      const int fixed =
+          conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, bn / ncta, 1, pbufs) - stage;
+      int stages = (kSmemLimit - fixed) / stage;
+      if (stages > kPatchMaxBStages) stages = kPatchMaxBStages;
+      if (stages >= 4 && bn >= 64) {
+        s.n_tiles = ceil_div(np, bn);
+        s.block_n = bn;
+        s.b_stages = stages;
+        s.p_bufs = pbufs;
+        s.ok = true;
+        return s;
+      }
     }
   }
   return s;
 }
 }  // namespace
 
-bool conv_patch_applicable(const ConvGeom& g) { return patch_shape(g).ok; }
-bool conv_patch_streams(const ConvGeom& g) {
-  const PatchShape s = patch_shape(g);
+bool conv_patch_applicable(const ConvGeom& g, int pair) { return patch_shape(g, pair).ok; }
+bool conv_patch_streams(const ConvGeom& g, int pair) {
+  const PatchShape s = patch_shape(g, pair);
   return s.ok && s.b_stages > 0;
 }
 
 bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                              const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                              const __nv_bfloat16* residual, bool relu, ConvPatchParams* out,
-                             std::string* err) {
-  const PatchShape s = patch_shape(g);
+                             std::string* err, int pair) {
+  const PatchShape s = patch_shape(g, pair);
   if (!s.ok) {
     if (err) *err = "conv_patch: geometry not supported";
     return false;
@@ -460,6 +470,8 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   p.n_tiles = s.n_tiles;
   p.block_n = s.block_n;
   p.b_stages = s.b_stages;
+  p.p_bufs = s.p_bufs;
+  p.pair = pair ? 1 : 0;
   p.tw = s.tw; p.th = s.th; p.tt = s.tt;
   p.lpw = s.lpw; p.lph = s.lph;
   p.tiles_w = ceil_div(g.Wo, s.tw);
@@ -484,7 +496,7 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   {
     const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)np};
     const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
-    const uint32_t box[2] = {64u, (uint32_t)s.block_n};
+    const uint32_t box[2] = {64u, (uint32_t)(s.block_n / (pair ? 2 : 1))};
     if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, 128, err)) return false;
   }
   return true;

@@ -53,16 +53,17 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                           const __nv_bfloat16* residual, bool relu, int num_sms, ConvTcParams* out,
                           std::string* err, int force_cm = 0, int force_cn = 0);
 
-// Patch kernel (conv_patch.cuh): applicable to stride-1 1x3x3 and 3x1x1 convolutions whose packed
-// weights fit in shared memory next to two activation patches.
-bool conv_patch_applicable(const ConvGeom& g);
+// Patch kernel (conv_patch.cuh): stride-1 1x3x3 and 3x1x1 convolutions; weights resident in shared
+// memory when they fit next to two activation patches, streamed otherwise.  pair = 1 plans the
+// CTA-pair (cta_group::2) variant, in which each CTA holds half of every weight tile.
+bool conv_patch_applicable(const ConvGeom& g, int pair = 0);
 // true when the patch kernel would have to stream its weights (they do not fit in shared memory);
 // then the tap kernel may be faster and the model times both
-bool conv_patch_streams(const ConvGeom& g);
+bool conv_patch_streams(const ConvGeom& g, int pair = 0);
 bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                              const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                              const __nv_bfloat16* residual, bool relu, ConvPatchParams* out,
-                             std::string* err);
+                             std::string* err, int pair = 0);
 
 uint16_t f32_to_bf16_bits(float f);
 float bf16_bits_to_f32(uint16_t b);

@@ -158,9 +158,11 @@ static bool run_case(const Case& c, int perf_iters) {
   bool patch_pass = true;
   if (conv_patch_applicable(g)) {
     patch_pass = false;
-    for (int mode = 0; mode < 1; ++mode) {
+    bool all_ok = true;
+    for (int mode = 0; mode < 2; ++mode) {
+      if (!conv_patch_applicable(g, mode)) continue;
       ConvPatchParams pp;
-      if (!build_conv_patch_params(g, B, dxb, dwp, dyb, dshift, drb, c.relu, &pp, &err)) {
+      if (!build_conv_patch_params(g, B, dxb, dwp, dyb, dshift, drb, c.relu, &pp, &err, mode)) {
         printf("    patch PLAN FAILED: %s\n", err.c_str());
         break;
       }
@@ -182,9 +184,10 @@ static bool run_case(const Case& c, int perf_iters) {
           if (!(e <= perr)) perr = e;
         }
       const bool ok = perr / (max_ref > 0 ? max_ref : 1) < 1e-2 && pbad == 0 && nanc == 0;
-      printf("    patch kernel (tile w%d h%d t%d, N=%dx%d, %s): max|err|=%.4f pad_bad=%zu nan=%zu  %s\n",
-             pp.tw, pp.th, pp.tt, pp.n_tiles, pp.block_n,
-             pp.b_stages ? "streamed weights" : "resident weights", perr, pbad, nanc,
+      printf("    patch kernel%s (tile w%d h%d t%d, N=%dx%d, %s, %d patch bufs, %d B stages): "
+             "max|err|=%.4f pad_bad=%zu nan=%zu  %s\n",
+             mode ? " CTA-PAIR" : "", pp.tw, pp.th, pp.tt, pp.n_tiles, pp.block_n,
+             pp.b_stages ? "streamed" : "resident", pp.p_bufs, pp.b_stages, perr, pbad, nanc,
              ok ? "PASS" : "FAIL");
       if (ok && perf_iters > 0) {
         cudaEvent_t e0, e1;
@@ -199,9 +202,11 @@ static bool run_case(const Case& c, int perf_iters) {
         CK(cudaEventElapsedTime(&ms, e0, e1));
         const double us = ms * 1e3 / perf_iters;
         printf("    patch perf: %.1f us  %.1f TFLOP/s\n", us, g.flops(B) / us * 1e-6);
+        fflush(stdout);
       }
-      patch_pass = patch_pass || ok;
+      all_ok = all_ok && ok;
     }
+    patch_pass = all_ok;
   }
 
   if (perf_iters > 0 && pass) {
