@@ -221,9 +221,11 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
       // previous tile's epilogue is not done by then and the MMA queue drains while the issuing
       // thread blocks.  profiles/r01_mma_issue_notes.md)
       for (int item = first_item; item < total_items; item += item_step, ++local) {
-        const PatchItem tc = decode_patch_item(p, item, kNumCta, 0);
-        const uint32_t idesc = kPair ? ptx::make_idesc_bf16_m256((uint32_t)tc.ncols)
-                                     : ptx::make_idesc_bf16_m128((uint32_t)tc.ncols);
+        // the issuing thread only needs the width of the channel tile, not the full tile decode
+        // (its integer divisions would sit on the critical path of every tile boundary)
+        const int ncols = kStream ? min(p.block_n, p.n - (item % p.n_tiles) * p.block_n) : p.n;
+        const uint32_t idesc = kPair ? ptx::make_idesc_bf16_m256((uint32_t)ncols)
+                                     : ptx::make_idesc_bf16_m128((uint32_t)ncols);
         const uint32_t acc = local & 1;
         const uint32_t acc_phase = (local >> 1) & 1;
         const uint32_t tmem_d = tmem_base + acc * kMaxBlockN;

@@ -182,13 +182,13 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
     uint32_t stage = 0, phase = 0;
     int local = 0;
     for (int item = first_item; item < items.total; item += item_step, ++local) {
-      int m, nt;
-      items.tile(item, &m, &nt);
-      const TileCoord tc = decode_tile(p, m, nt);
-      const bool live = tc.ncols > 0;  // padding CTA of a cluster: keeps the barriers moving only
+      // the issuing thread only needs the width of the channel tile, not the full tile decode
+      const int nt = (item % items.n_groups) * items.cn + items.rn;
+      const int ncols = min(p.block_n, p.cout_pad - nt * p.block_n);
+      const bool live = ncols > 0;  // padding CTA of a cluster: keeps the barriers moving only
       const uint32_t acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
-      const uint32_t idesc = ptx::make_idesc_bf16_m128((uint32_t)(live ? tc.ncols : 16));
+      const uint32_t idesc = ptx::make_idesc_bf16_m128((uint32_t)(live ? ncols : 16));
       const uint32_t tmem_d = tmem_base + acc * kMaxBlockN;
       ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1);
       ptx::tc_fence_after();
