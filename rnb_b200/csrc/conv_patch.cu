@@ -14,6 +14,7 @@
 #include <stdio.h>
 
 #include "conv_patch.cuh"
+#include "epilogue.cuh"
 #include "ptx.cuh"
 
 namespace rnb {
@@ -55,11 +56,38 @@ __device__ __forceinline__ PatchItem decode_patch_item(const ConvPatchParams& p,
 // reads 64*(M+N)/N B/clk plus TMA fills against a 128 B/clk port).  The leader (rank 0) issues all
 // MMAs; both CTAs' TMA loads signal the leader's "full" barriers, the leader's commits release the
 // buffers and publish the accumulators in both CTAs.
+#ifdef RNB_PATCH_COUNTERS
+// development aid (make test_conv_cnt): cycles CTA 0's warps spend waiting, summed over its tiles
+__device__ unsigned long long g_patch_cnt[8];
+__device__ unsigned long long g_patch_epi[8];
+__device__ unsigned long long g_patch_cta[4][3][256];  // per CTA: globaltimer at entry, MMA loop start/end
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// (accumulated in registers, written once when the role ends: a global read-modify-write per
+// wait would itself stall the warp being measured)
+#define CNT_DECL() unsigned long long cnt_acc[6] = {}
+#define CNT_BEGIN() const long long cnt_t0 = clock64()
+#define CNT_END(i) cnt_acc[i] += (unsigned long long)(clock64() - cnt_t0)
+#define CNT_FLUSH(i) \
+  if (blockIdx.x == 0 && lane == 0) g_patch_cnt[i] += cnt_acc[i]
+#else
+#define CNT_DECL()
+#define CNT_BEGIN()
+#define CNT_END(i)
+#define CNT_FLUSH(i)
+#endif
+
 template <bool kRes, bool kRelu, bool kStream, bool kPair>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+#ifdef RNB_PATCH_COUNTERS
+  if (threadIdx.x == 0 && blockIdx.x < 256) g_patch_cta[p.dbg_launch & 3][0][blockIdx.x] = gtimer();
+#endif
   // shuffle-broadcast so the compiler knows these are warp-uniform (role branches, TMEM address)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -112,7 +140,7 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
       ptx::mbar_init(tmem_full_bar + 8 * s, 1);
       // pair mode: one arrival per CTA (its epilogue warps meet on a named barrier first) --
       // hundreds of remote arrivals per tile on one mbarrier serialise
-      ptx::mbar_init(tmem_empty_bar + 8 * s, kPair ? 2 : kEpiThreads);
+      ptx::mbar_init(tmem_empty_bar + 8 * s, kPair ? 2 : kEpiThreads / 32);
     }
     for (int s = 0; s < kPatchMaxBStages; ++s) {
       ptx::mbar_init(b_full + 8 * s, 1);
@@ -148,6 +176,7 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   asm volatile("ld.shared.b32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
   tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
 
+  CNT_DECL();
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (warp-wide)
     if (!kStream) {
@@ -171,7 +200,23 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     uint32_t bs = 0, bphase = 0;
     for (int item = first_item; item < total_items; item += item_step) {
       const PatchItem tc = decode_patch_item(p, item, kNumCta, rank);
-      ptx::mbar_wait(p_empty + 8 * pb, ph ^ 1);
+      // L2 prefetch of the patch `p.prefetch` items ahead: its real load can only be issued when a
+      // patch buffer frees, about one tile before it is needed, which is less than the DRAM
+      // latency; with the prefetch that load hits L2
+      if (p.prefetch > 0) {
+        const int ahead = item + p.prefetch * item_step;
+        if (ahead < total_items) {
+          const PatchItem ta = decode_patch_item(p, ahead, kNumCta, rank);
+          for (int kb = 0; kb < p.nkb; ++kb)
+            ptx::tma_prefetch_5d_elect(&p.a_map, kb * 64, ta.w0 + p.aw, ta.h0 + p.ah, ta.t0 + p.at,
+                                       ta.b);
+        }
+      }
+      {
+        CNT_BEGIN();
+        ptx::mbar_wait(p_empty + 8 * pb, ph ^ 1);
+        CNT_END(0);
+      }
       if (rank == 0) ptx::mbar_expect_tx_elect(p_full + 8 * pb, kNumCta * patch_bytes);
       for (int kb = 0; kb < p.nkb; ++kb) {
         const uint32_t dst = pbuf + pb * patch_bytes + kb * pblock_bytes;
@@ -207,12 +252,18 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
         ph ^= 1;
       }
     }
+    CNT_FLUSH(0);
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (warp-wide)
     // (reads only shared memory and TMEM: ordered behind the producer's grid_dep_wait by the
     // patch-full barrier).  In pair mode only the leader issues.
     if (!kPair || rank == 0) {
       if (!kStream) ptx::mbar_wait(w_full, 0);
+#ifdef RNB_PATCH_COUNTERS
+      if (lane == 0 && blockIdx.x < 256) g_patch_cta[p.dbg_launch & 3][1][blockIdx.x] = gtimer();
+      const long long loop_c0 = clock64();
+      const unsigned long long loop_g0 = gtimer();
+#endif
       int local = 0;
       uint32_t pb = 0, ph = 0;
       uint32_t bs = 0, bphase = 0;
@@ -229,9 +280,18 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
         const uint32_t acc = local & 1;
         const uint32_t acc_phase = (local >> 1) & 1;
         const uint32_t tmem_d = tmem_base + acc * kMaxBlockN;
-        ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1);
-        ptx::mbar_wait(p_full + 8 * pb, ph);
+        {
+          CNT_BEGIN();
+          ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1);
+          CNT_END(1);
+        }
+        {
+          CNT_BEGIN();
+          ptx::mbar_wait(p_full + 8 * pb, ph);
+          CNT_END(2);
+        }
         ptx::tc_fence_after();
+        CNT_BEGIN();
         uint32_t accumulate = 0;
         uint32_t wt = wbuf;
         for (int tap = 0; tap < p.num_taps; ++tap) {
@@ -278,11 +338,21 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
           ptx::umma_commit_elect(p_empty + 8 * pb);
           ptx::umma_commit_elect(tmem_full_bar + 8 * acc);
         }
+        CNT_END(3);
         if (++pb == (uint32_t)p.p_bufs) {
           pb = 0;
           ph ^= 1;
         }
       }
+      CNT_FLUSH(1);
+      CNT_FLUSH(2);
+      CNT_FLUSH(3);
+#ifdef RNB_PATCH_COUNTERS
+      if (blockIdx.x == 0 && lane == 0) {
+        g_patch_cnt[6] += (unsigned long long)(clock64() - loop_c0);
+        g_patch_cnt[7] += gtimer() - loop_g0;
+      }
+#endif
     }
   } else {
     // ------------------------------------------------------------------ epilogue (256 threads)
@@ -298,72 +368,99 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     const bool in_tile = (rw < p.tw) && (rh < p.th) && (rt < p.tt);
     int local = 0;
     int table_n0 = kStream ? -1 : 0;
-    for (int item = first_item; item < total_items; item += item_step, ++local) {
+#ifdef RNB_PATCH_COUNTERS
+    unsigned long long epi_cnt[6] = {};
+#endif
+    // this thread's slice of a work item: where its output row lives and whether it exists
+    struct Slice {
+      size_t off;
+      int n0, ncols;
+      bool valid;
+    };
+    auto slice_of = [&](int item) {
       const PatchItem tc = decode_patch_item(p, item, kNumCta, rank);
+      const int w = tc.w0 + rw, h = tc.h0 + rh, t = tc.t0 + rt;
+      Slice s;
+      s.valid = in_tile && (w < p.Wo) && (h < p.Ho) && (t < p.To) && (tc.b < p.B);
+      s.off = ((((size_t)tc.b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad + tc.n0;
+      s.n0 = tc.n0;
+      s.ncols = tc.ncols;
+      return s;
+    };
+    // One work item.  The residual rows of the item after the next are prefetched into L2 before
+    // the wait for this item's accumulator, two tile periods ahead of their use (one period is
+    // about one loaded DRAM round trip, which is not enough).
+    auto one_item = [&](int item, const Slice& cur, const Slice& nxt) {
       const uint32_t acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
-      const int w = tc.w0 + rw, h = tc.h0 + rh, t = tc.t0 + rt;
-      const bool valid = in_tile && (w < p.Wo) && (h < p.Ho) && (t < p.To) && (tc.b < p.B);
-      const size_t off =
-          ((((size_t)tc.b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad + tc.n0;
-      __nv_bfloat16* out_row = p.y + off;
-      const __nv_bfloat16* res_row = kRes ? p.residual + off : nullptr;
-      if (kStream && tc.n0 != table_n0) {
+      Slice nxt2 = nxt;
+      if (item + 2 * item_step < total_items) {
+        nxt2 = slice_of(item + 2 * item_step);
+        if (kRes) prefetch_residual_l2(p.residual + nxt2.off, nxt2.ncols, nxt2.valid);
+      }
+      if (kStream && cur.n0 != table_n0) {
         // shift table of this channel tile; the barriers order it against the previous readers
         ptx::named_bar_sync(1, kEpiThreads);
-        if (et < tc.ncols) {
-          const float v = __ldg(p.shift + tc.n0 + et);
+        if (et < cur.ncols) {
+          const float v = __ldg(p.shift + cur.n0 + et);
           asm volatile("st.shared.f32 [%0], %1;\n" ::"r"(shift_tab + et * 4), "f"(v) : "memory");
         }
         ptx::named_bar_sync(1, kEpiThreads);
-        table_n0 = tc.n0;
+        table_n0 = cur.n0;
       }
-      ptx::mbar_wait(tmem_full_bar + 8 * acc, acc_phase);
-      ptx::tc_fence_after();
+      CNT_BEGIN();
       const uint32_t taddr_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kMaxBlockN;
-      const int nchunk = tc.ncols >> 4;
-      for (int cchunk = half; cchunk < nchunk; cchunk += 2) {
-        uint32_t v[16];
-        const int col = cchunk * 16;
-        ptx::tmem_ld16(taddr_row + col, v);
-        uint64_t sh2[8];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];\n"
-                       : "=l"(sh2[2 * j]), "=l"(sh2[2 * j + 1])
-                       : "r"(shift_tab + (col + 4 * j) * 4));
-        }
-        uint32_t rwd[8];
-        if (kRes) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) rwd[j] = 0u;
-          if (valid) ptx::ld_global_nc_v8(res_row + col, rwd);
-        }
-        ptx::tmem_ld_wait();
-        uint32_t o[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          uint64_t x = ptx::add_f32x2(
-              ptx::pack_f32x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), sh2[j]);
-          if (kRes)
-            x = ptx::add_f32x2(x, ptx::pack_f32x2(__uint_as_float(rwd[j] << 16),
-                                                  __uint_as_float(rwd[j] & 0xffff0000u)));
-          o[j] = ptx::cvt_bf16x2<kRelu>(x);
-        }
-        if (valid) ptx::st_global_v8(out_row + col, o);
-      }
+      epilogue_tile<kRes, kRelu>(tmem_full_bar + 8 * acc, acc_phase, taddr_row, shift_tab,
+                                 cur.ncols >> 4, half, cur.valid, p.y + cur.off,
+                                 kRes ? p.residual + cur.off : nullptr
+#ifdef RNB_PATCH_COUNTERS
+                                 ,
+                                 epi_cnt
+#endif
+      );
+      // every TMEM read of this accumulator buffer has completed: hand it back, one arrival per
+      // warp (hundreds of arrivals per tile on one mbarrier serialise)
       ptx::tc_fence_before();
+      __syncwarp();
       if (kPair) {
         ptx::named_bar_sync(2, kEpiThreads);
         if (et == 0) ptx::mbar_arrive_cluster(tmem_empty_ld + 8 * acc);
       } else {
-        ptx::mbar_arrive(tmem_empty_bar + 8 * acc);
+        if (lane == 0) ptx::mbar_arrive(tmem_empty_bar + 8 * acc);
       }
+      CNT_END(5);
+      ++local;
+      return nxt2;
+    };
+    Slice cur = {}, nxt = {};
+    if (first_item < total_items) {
+      cur = slice_of(first_item);
+      if (kRes) prefetch_residual_l2(p.residual + cur.off, cur.ncols, cur.valid);
     }
+    if (first_item + item_step < total_items) {
+      nxt = slice_of(first_item + item_step);
+      if (kRes) prefetch_residual_l2(p.residual + nxt.off, nxt.ncols, nxt.valid);
+    }
+    for (int item = first_item; item < total_items; item += item_step) {
+      const Slice nxt2 = one_item(item, cur, nxt);
+      cur = nxt;
+      nxt = nxt2;
+    }
+    if (warp == 2) {
+      CNT_FLUSH(4);
+      CNT_FLUSH(5);
+    }
+#ifdef RNB_PATCH_COUNTERS
+    if (blockIdx.x == 0 && warp == 2 && lane == 0)
+      for (int k = 0; k < 6; ++k) g_patch_epi[k] += epi_cnt[k];
+#endif
   }
 
   ptx::tc_fence_before();
   __syncthreads();
+#ifdef RNB_PATCH_COUNTERS
+  if (threadIdx.x == 0 && blockIdx.x < 256) g_patch_cta[p.dbg_launch & 3][2][blockIdx.x] = gtimer();
+#endif
   // the leader's last commits may still be on their way to the peer's barriers
   if (kPair) ptx::cluster_sync_all();
   if (warp == 1) {
@@ -374,6 +471,22 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
       ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
 }
+
+#ifdef RNB_PATCH_COUNTERS
+void patch_cta_times(unsigned long long out[4][3][256]) {
+  cudaMemcpyFromSymbol(out, g_patch_cta, sizeof(g_patch_cta));
+}
+void patch_counters_read_reset(unsigned long long out[8]) {
+  cudaMemcpyFromSymbol(out, g_patch_cnt, sizeof(g_patch_cnt));
+  unsigned long long z[8] = {};
+  cudaMemcpyToSymbol(g_patch_cnt, z, sizeof(z));
+}
+void patch_epi_read_reset(unsigned long long out[8]) {
+  cudaMemcpyFromSymbol(out, g_patch_epi, sizeof(g_patch_epi));
+  unsigned long long z[8] = {};
+  cudaMemcpyToSymbol(g_patch_epi, z, sizeof(z));
+}
+#endif
 
 namespace {
 template <bool kRes, bool kRelu, bool kStream, bool kPair>

@@ -14,6 +14,7 @@
 #include <stdio.h>
 
 #include "conv_tc.cuh"
+#include "epilogue.cuh"
 #include "ptx.cuh"
 
 namespace rnb {
@@ -108,7 +109,7 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(tmem_full_bar + 8 * s, 1);
-      ptx::mbar_init(tmem_empty_bar + 8 * s, kEpiThreads);
+      ptx::mbar_init(tmem_empty_bar + 8 * s, kEpiThreads / 32);
     }
     ptx::fence_mbar_init();
   }
@@ -239,65 +240,79 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
     const int ib = row >> lbb_shift;
     int local = 0;
     int table_n0 = -1;
-    for (int item = first_item; item < items.total; item += item_step, ++local) {
+#ifdef RNB_PATCH_COUNTERS
+    unsigned long long epi_cnt[6] = {};  // (only the patch kernel reports them)
+#endif
+    // this thread's slice of a work item: where its output row lives and whether it exists
+    struct Slice {
+      size_t off;
+      int n0, ncols;
+      bool valid;
+    };
+    auto slice_of = [&](int item) {
       int m, nt;
       items.tile(item, &m, &nt);
       const TileCoord tc = decode_tile(p, m, nt);
+      const int w = tc.w0 + iw, h = tc.h0 + ih, t = tc.t0 + it, b = tc.b0 + ib;
+      Slice s;
+      s.valid = (w < p.Wo) && (h < p.Ho) && (t < p.To) && (b < p.B);
+      s.off = ((((size_t)b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad + tc.n0;
+      s.n0 = tc.n0;
+      s.ncols = tc.ncols > 0 ? tc.ncols : 0;
+      return s;
+    };
+    // One work item.  The residual rows of the item after the next are prefetched into L2 before
+    // the wait for this item's accumulator, two tile periods ahead of their use (one period is
+    // about one loaded DRAM round trip, which is not enough).
+    auto one_item = [&](int item, const Slice& cur, const Slice& nxt) {
       const uint32_t acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
-      const int w = tc.w0 + iw, h = tc.h0 + ih, t = tc.t0 + it, b = tc.b0 + ib;
-      const bool valid = (w < p.Wo) && (h < p.Ho) && (t < p.To) && (b < p.B);
-      const size_t off = ((((size_t)b * p.To + t) * p.Ho + h) * p.Wo + w) * p.cout_pad + tc.n0;
-      __nv_bfloat16* out_row = p.y + off;
-      const __nv_bfloat16* res_row = kRes ? p.residual + off : nullptr;
-      if (tc.n0 != table_n0) {
+      Slice nxt2 = nxt;
+      if (item + 2 * item_step < items.total) {
+        nxt2 = slice_of(item + 2 * item_step);
+        if (kRes) prefetch_residual_l2(p.residual + nxt2.off, nxt2.ncols, nxt2.valid);
+      }
+      if (cur.n0 != table_n0) {
         // per-channel shift of this channel tile -> shared memory.  The barrier before the write
         // keeps it behind the previous tile's readers, the one after publishes it.
         ptx::named_bar_sync(1, kEpiThreads);
-        if (et < tc.ncols) {
-          const float v = __ldg(p.shift + tc.n0 + et);
+        if (et < cur.ncols) {
+          const float v = __ldg(p.shift + cur.n0 + et);
           asm volatile("st.shared.f32 [%0], %1;\n" ::"r"(shift_tab + et * 4), "f"(v) : "memory");
         }
         ptx::named_bar_sync(1, kEpiThreads);
-        table_n0 = tc.n0;
+        table_n0 = cur.n0;
       }
-      ptx::mbar_wait(tmem_full_bar + 8 * acc, acc_phase);
-      ptx::tc_fence_after();
       const uint32_t taddr_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kMaxBlockN;
-      const int nchunk = tc.ncols > 0 ? tc.ncols >> 4 : 0;
-      for (int cchunk = half; cchunk < nchunk; cchunk += 2) {
-        uint32_t v[16];
-        const int col = cchunk * 16;
-        ptx::tmem_ld16(taddr_row + col, v);
-        uint64_t sh2[8];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];\n"
-                       : "=l"(sh2[2 * j]), "=l"(sh2[2 * j + 1])
-                       : "r"(shift_tab + (col + 4 * j) * 4));
-        }
-        uint32_t rwd[8];
-        if (kRes) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) rwd[j] = 0u;
-          if (valid) ptx::ld_global_nc_v8(res_row + col, rwd);
-        }
-        ptx::tmem_ld_wait();
-        uint32_t o[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          uint64_t x = ptx::add_f32x2(
-              ptx::pack_f32x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), sh2[j]);
-          if (kRes)
-            x = ptx::add_f32x2(x, ptx::pack_f32x2(__uint_as_float(rwd[j] << 16),
-                                                  __uint_as_float(rwd[j] & 0xffff0000u)));
-          o[j] = ptx::cvt_bf16x2<kRelu>(x);
-        }
-        if (valid) ptx::st_global_v8(out_row + col, o);
-      }
-      // every TMEM read of this accumulator buffer has completed: hand it back to the MMA warp
+      epilogue_tile<kRes, kRelu>(tmem_full_bar + 8 * acc, acc_phase, taddr_row, shift_tab,
+                                 cur.ncols >> 4, half, cur.valid, p.y + cur.off,
+                                 kRes ? p.residual + cur.off : nullptr
+#ifdef RNB_PATCH_COUNTERS
+                                 ,
+                                 epi_cnt
+#endif
+      );
+      // every TMEM read of this accumulator buffer has completed: hand it back to the MMA warp,
+      // one arrival per warp
       ptx::tc_fence_before();
-      ptx::mbar_arrive(tmem_empty_bar + 8 * acc);
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(tmem_empty_bar + 8 * acc);
+      ++local;
+      return nxt2;
+    };
+    Slice cur = {}, nxt = {};
+    if (first_item < items.total) {
+      cur = slice_of(first_item);
+      if (kRes) prefetch_residual_l2(p.residual + cur.off, cur.ncols, cur.valid);
+    }
+    if (first_item + item_step < items.total) {
+      nxt = slice_of(first_item + item_step);
+      if (kRes) prefetch_residual_l2(p.residual + nxt.off, nxt.ncols, nxt.valid);
+    }
+    for (int item = first_item; item < items.total; item += item_step) {
+      const Slice nxt2 = one_item(item, cur, nxt);
+      cur = nxt;
+      nxt = nxt2;
     }
   }
 

@@ -5,6 +5,7 @@
 #include <stdlib.h>
 
 #include <string>
+#include <algorithm>
 #include <vector>
 
 #include "conv_tc.cuh"
@@ -12,6 +13,13 @@
 #include "plan.cuh"
 
 using namespace rnb;
+#ifdef RNB_PATCH_COUNTERS
+namespace rnb {
+void patch_counters_read_reset(unsigned long long out[8]);
+void patch_epi_read_reset(unsigned long long out[8]);
+void patch_cta_times(unsigned long long out[4][3][256]);
+}
+#endif
 
 #define CK(x)                                                                      \
   do {                                                                             \
@@ -202,6 +210,59 @@ static bool run_case(const Case& c, int perf_iters) {
         CK(cudaEventElapsedTime(&ms, e0, e1));
         const double us = ms * 1e3 / perf_iters;
         printf("    patch perf: %.1f us  %.1f TFLOP/s\n", us, g.flops(B) / us * 1e-6);
+#ifdef RNB_PATCH_COUNTERS
+        {
+          unsigned long long cnt[8];
+          unsigned long long ec[8];
+          patch_counters_read_reset(cnt);
+          patch_epi_read_reset(ec);
+          CK(launch_conv_patch(pp, num_sms, 0));
+          CK(cudaDeviceSynchronize());
+          patch_counters_read_reset(cnt);
+          patch_epi_read_reset(ec);
+          const int tiles = pp.tiles_w * pp.tiles_h * pp.tiles_t * pp.tiles_b;
+          const double it = (double)((tiles + (mode ? 1 : 0)) / (mode ? 2 : 1)) * pp.n_tiles /
+                            (num_sms / (mode ? 2 : 1));
+          printf("    CTA 0 cycles per item (%.1f items): producer wait p_empty %.0f | mma wait "
+                 "tmem_empty %.0f, wait p_full %.0f, issue %.0f | epi wait tmem_full %.0f, work %.0f\n",
+                 it, cnt[0] / it, cnt[1] / it, cnt[2] / it, cnt[3] / it, cnt[4] / it, cnt[5] / it);
+          printf("      epilogue warp 2 of CTA 0, cycles per item: residual issue %.0f | wait tmem_full "
+                 "%.0f | issue tcgen05.ld %.0f | shift/next-residual loads %.0f | wait tcgen05.ld %.0f | "
+                 "convert + store %.0f\n",
+                 ec[0] / it, ec[1] / it, ec[5] / it, ec[2] / it, ec[3] / it, ec[4] / it);
+          printf("      MMA loop of CTA 0: %llu cycles in %.1f us = %.0f MHz SM clock\n", cnt[6],
+                 cnt[7] * 1e-3, (double)cnt[6] / (cnt[7] * 1e-3));
+          static unsigned long long ct[4][3][256];
+          // 8 back-to-back launches; the last 4 leave their per-CTA timestamps
+          pp.dbg_launch = 0;
+          for (int i = 0; i < 8; ++i) {
+            pp.dbg_launch = i & 3;
+            CK(launch_conv_patch(pp, num_sms, 0));
+          }
+          CK(cudaDeviceSynchronize());
+          patch_cta_times(ct);
+          const int nc = num_sms < 256 ? num_sms : 256;
+          unsigned long long base = ~0ull;
+          for (int i = 0; i < nc; ++i)
+            if (ct[0][0][i] < base) base = ct[0][0][i];
+          for (int l = 0; l < 4; ++l) {
+            std::vector<double> entry, start, end;
+            for (int i = 0; i < nc; i += mode ? 2 : 1) {
+              entry.push_back((double)(long long)(ct[l][0][i] - base) * 1e-3);
+              start.push_back((double)(long long)(ct[l][1][i] - base) * 1e-3);
+              end.push_back((double)(long long)(ct[l][2][i] - base) * 1e-3);
+            }
+            std::sort(entry.begin(), entry.end());
+            std::sort(start.begin(), start.end());
+            std::sort(end.begin(), end.end());
+            const size_t n = entry.size();
+            printf("      launch %d (us): entry %.1f/%.1f/%.1f  mma start %.1f/%.1f/%.1f  exit "
+                   "%.1f/%.1f/%.1f  (min/med/max)\n",
+                   l, entry[0], entry[n / 2], entry[n - 1], start[0], start[n / 2], start[n - 1],
+                   end[0], end[n / 2], end[n - 1]);
+          }
+        }
+#endif
         fflush(stdout);
       }
       all_ok = all_ok && ok;
@@ -341,6 +402,7 @@ int main(int argc, char** argv) {
       {"conv5 spatial 512->1152", geom(1, 7, 7, 512, 1152, 1, 3, 3, 1, 1, 1, 0, 1, 1), 3, true, false},
       {"conv5 temporal 1152->512 +res", geom(1, 7, 7, 1152, 512, 3, 1, 1, 1, 1, 1, 1, 0, 0), 3, true, true},
       {"stem temporal 83->64", geom(8, 56, 56, 83, 64, 3, 1, 1, 1, 1, 1, 1, 0, 0), 1, false, false},
+      {"conv2 temporal 144->64", geom(8, 56, 56, 144, 64, 3, 1, 1, 1, 1, 1, 1, 0, 0), 1, true, false},
   };
   int failed = 0;
   for (const Case& c : cases) failed += run_case(c, 0) ? 0 : 1;
