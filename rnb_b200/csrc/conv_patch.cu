@@ -60,7 +60,8 @@ __device__ __forceinline__ PatchItem decode_patch_item(const ConvPatchParams& p,
 // development aid (make test_conv_cnt): cycles CTA 0's warps spend waiting, summed over its tiles
 __device__ unsigned long long g_patch_cnt[8];
 __device__ unsigned long long g_patch_epi[8];
-__device__ unsigned long long g_patch_cta[4][3][256];  // per CTA: globaltimer at entry, MMA loop start/end
+__device__ unsigned long long g_patch_cta[4][3][256];
+__device__ unsigned int g_patch_smid[4][256];  // per CTA: globaltimer at entry, MMA loop start/end
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -86,7 +87,12 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
 #ifdef RNB_PATCH_COUNTERS
-  if (threadIdx.x == 0 && blockIdx.x < 256) g_patch_cta[p.dbg_launch & 3][0][blockIdx.x] = gtimer();
+  if (threadIdx.x == 0 && blockIdx.x < 256) {
+    g_patch_cta[p.dbg_launch & 3][0][blockIdx.x] = gtimer();
+    unsigned int smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    g_patch_smid[p.dbg_launch & 3][blockIdx.x] = smid;
+  }
 #endif
   // shuffle-broadcast so the compiler knows these are warp-uniform (role branches, TMEM address)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
@@ -123,7 +129,6 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   const int first_item = blockIdx.x / kNumCta;
   const int item_step = gridDim.x / kNumCta;
   // barriers the MMA warp waits on live in the leader; both CTAs' loads signal them
-  const uint32_t w_full_ld = kPair ? ptx::map_to_cta(w_full, 0) : w_full;
   const uint32_t p_full_ld = kPair ? ptx::map_to_cta(p_full, 0) : p_full;
   const uint32_t b_full_ld = kPair ? ptx::map_to_cta(b_full, 0) : b_full;
   const uint32_t tmem_empty_ld = kPair ? ptx::map_to_cta(tmem_empty_bar, 0) : tmem_empty_bar;
@@ -183,17 +188,22 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
       // the packed weights are constants of the model: fetch them while the previous kernel in
       // the stream is still draining, and only then wait for its activations.  In pair mode the
       // leader announces the bytes of BOTH halves; each CTA fetches its own rows.
-      if (rank == 0) ptx::mbar_expect_tx_elect(w_full, kNumCta * n_wtiles * wtile_bytes);
+      // One barrier per tap (the stream-mode weight barriers are free in this mode): the first
+      // tile starts on tap 0 while the other taps are still arriving, instead of idling for the
+      // ~2 us the whole weight set takes at the SM's inbound TMA rate.
       const int row0 = rank * (p.n / kNumCta);
-      for (int tap = 0, i = 0; tap < p.num_taps; ++tap)
+      for (int tap = 0, i = 0; tap < p.num_taps; ++tap) {
+        if (rank == 0)
+          ptx::mbar_expect_tx_elect(b_full + 8 * tap, kNumCta * p.nkb * wtile_bytes);
         for (int kb = 0; kb < p.nkb; ++kb, ++i) {
           if (kPair)
-            ptx::tma_load_2d_pair_elect(wbuf + i * wtile_bytes, &p.b_map, w_full_ld,
+            ptx::tma_load_2d_pair_elect(wbuf + i * wtile_bytes, &p.b_map, b_full_ld + 8 * tap,
                                         tap * p.cin_pad + kb * 64, row0);
           else
-            ptx::tma_load_2d_elect(wbuf + i * wtile_bytes, &p.b_map, w_full,
+            ptx::tma_load_2d_elect(wbuf + i * wtile_bytes, &p.b_map, b_full + 8 * tap,
                                    tap * p.cin_pad + kb * 64, 0);
         }
+      }
     }
     ptx::grid_dep_wait();
     uint32_t pb = 0, ph = 0;
@@ -258,7 +268,6 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     // (reads only shared memory and TMEM: ordered behind the producer's grid_dep_wait by the
     // patch-full barrier).  In pair mode only the leader issues.
     if (!kPair || rank == 0) {
-      if (!kStream) ptx::mbar_wait(w_full, 0);
 #ifdef RNB_PATCH_COUNTERS
       if (lane == 0 && blockIdx.x < 256) g_patch_cta[p.dbg_launch & 3][1][blockIdx.x] = gtimer();
       const long long loop_c0 = clock64();
@@ -296,6 +305,10 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
         uint32_t wt = wbuf;
         for (int tap = 0; tap < p.num_taps; ++tap) {
           const uint32_t arow = pbuf + pb * patch_bytes + (uint32_t)p.tap_shift[tap] * 128u;
+          if (!kStream && local == 0) {  // resident weights: tap by tap during the first tile
+            ptx::mbar_wait(b_full + 8 * tap, 0);
+            ptx::tc_fence_after();
+          }
           for (int kb = 0; kb < p.nkb; ++kb) {
             if (kStream) {
               ptx::mbar_wait(b_full + 8 * bs, bphase);
@@ -453,14 +466,14 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
 #ifdef RNB_PATCH_COUNTERS
     if (blockIdx.x == 0 && warp == 2 && lane == 0)
       for (int k = 0; k < 6; ++k) g_patch_epi[k] += epi_cnt[k];
+#ifdef RNB_EXIT_FENCE
+    __threadfence();  // experiment: is the exit->entry turnaround the drain of the output stores?
+#endif
 #endif
   }
 
   ptx::tc_fence_before();
   __syncthreads();
-#ifdef RNB_PATCH_COUNTERS
-  if (threadIdx.x == 0 && blockIdx.x < 256) g_patch_cta[p.dbg_launch & 3][2][blockIdx.x] = gtimer();
-#endif
   // the leader's last commits may still be on their way to the peer's barriers
   if (kPair) ptx::cluster_sync_all();
   if (warp == 1) {
@@ -469,12 +482,21 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
       ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
     else
       ptx::tmem_dealloc(tmem_base, kTmemCols);
+#ifdef RNB_PATCH_COUNTERS
+    // (replaces the exit stamp: is the turnaround to the next kernel's CTA spent in the dealloc?)
+    // (the CTA's exit stamp; a stamp taken by thread 0 right after the __syncthreads above was
+    // seen to be hoisted over it and showed the PRODUCER's finish time, several us early)
+    if (lane == 0 && blockIdx.x < 256) g_patch_cta[p.dbg_launch & 3][2][blockIdx.x] = gtimer();
+#endif
   }
 }
 
 #ifdef RNB_PATCH_COUNTERS
 void patch_cta_times(unsigned long long out[4][3][256]) {
   cudaMemcpyFromSymbol(out, g_patch_cta, sizeof(g_patch_cta));
+}
+void patch_cta_smids(unsigned int out[4][256]) {
+  cudaMemcpyFromSymbol(out, g_patch_smid, sizeof(g_patch_smid));
 }
 void patch_counters_read_reset(unsigned long long out[8]) {
   cudaMemcpyFromSymbol(out, g_patch_cnt, sizeof(g_patch_cnt));

@@ -408,7 +408,8 @@ PatchShape patch_shape(const ConvGeom& g, int pair) {
   if (s.eff < 0.6) return s;
   s.patch_rows = s.pbw * s.pbh * s.pbt;
   // weights resident if they fit next to two patches, otherwise streamed per channel tile
-  if (np <= kMaxBlockN &&
+  // (resident mode signals each tap's weights on one of the 2 * kPatchMaxBStages stream barriers)
+  if (np <= kMaxBlockN && s.taps <= 2 * kPatchMaxBStages &&
       conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np / ncta, 0) <= kSmemLimit) {
     s.n_tiles = 1;
     s.block_n = np;

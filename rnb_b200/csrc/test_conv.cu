@@ -18,6 +18,7 @@ namespace rnb {
 void patch_counters_read_reset(unsigned long long out[8]);
 void patch_epi_read_reset(unsigned long long out[8]);
 void patch_cta_times(unsigned long long out[4][3][256]);
+void patch_cta_smids(unsigned int out[4][256]);
 }
 #endif
 
@@ -197,7 +198,7 @@ static bool run_case(const Case& c, int perf_iters) {
              mode ? " CTA-PAIR" : "", pp.tw, pp.th, pp.tt, pp.n_tiles, pp.block_n,
              pp.b_stages ? "streamed" : "resident", pp.p_bufs, pp.b_stages, perr, pbad, nanc,
              ok ? "PASS" : "FAIL");
-      if (ok && perf_iters > 0) {
+      if ((ok || getenv("RNB_FORCE_PERF")) && perf_iters > 0) {
         cudaEvent_t e0, e1;
         CK(cudaEventCreate(&e0));
         CK(cudaEventCreate(&e1));
@@ -245,6 +246,25 @@ static bool run_case(const Case& c, int perf_iters) {
           unsigned long long base = ~0ull;
           for (int i = 0; i < nc; ++i)
             if (ct[0][0][i] < base) base = ct[0][0][i];
+          if (!mode) {
+            // per SM: time between the exit of launch l's CTA and the entry of launch l+1's CTA
+            static unsigned int sm[4][256];
+            patch_cta_smids(sm);
+            std::vector<double> turn;
+            int same_cta = 0;
+            for (int l = 0; l < 3; ++l)
+              for (int i = 0; i < nc; ++i)
+                for (int j = 0; j < nc; ++j)
+                  if (sm[l + 1][j] == sm[l][i]) {
+                    turn.push_back((double)(long long)(ct[l + 1][0][j] - ct[l][2][i]) * 1e-3);
+                    same_cta += (i == j);
+                  }
+            std::sort(turn.begin(), turn.end());
+            if (!turn.empty())
+              printf("      per-SM turnaround exit->next entry (us): min %.2f  med %.2f  max %.2f  "
+                     "(%zu pairs, %d with the same CTA index)\n",
+                     turn[0], turn[turn.size() / 2], turn.back(), turn.size(), same_cta);
+          }
           for (int l = 0; l < 4; ++l) {
             std::vector<double> entry, start, end;
             for (int i = 0; i < nc; i += mode ? 2 : 1) {
@@ -408,7 +428,7 @@ int main(int argc, char** argv) {
   for (const Case& c : cases) failed += run_case(c, 0) ? 0 : 1;
   failed += run_stem(2) ? 0 : 1;
 
-  if (perf_batch > 0 && failed == 0) {
+  if (perf_batch > 0 && (failed == 0 || getenv("RNB_FORCE_PERF"))) {
     printf("---- perf at B=%d\n", perf_batch);
     for (Case c : cases) {
       if (c.g.Hi < 7 || c.g.Hi == 8) continue;
