@@ -14,6 +14,7 @@ constexpr int kTmemCols = 512;       // two accumulator buffers
 constexpr int kConvThreads = 320;    // warp0 TMA, warp1 MMA, warps2-9 epilogue
 constexpr int kEpiThreads = 256;
 constexpr int kSmemLimit = 232448;   // 227 KB
+constexpr int kMaxSplitK = 8;        // portable cluster size
 
 // One output tile is a box of 128 output positions (bw x bh x bt x bb, powers of two) by up to
 // block_n output channels.  K runs over `num_taps` filter taps times cin_pad input channels; tap i
@@ -40,6 +41,9 @@ struct ConvTcParams {
   // same position tile and each fetch 1/cn of the activation tile (split along box dimension
   // a_slice_dim: 0 = w, 1 = h, 2 = t, 3 = b).  cm = cn = 1: no cluster.
   int cm, cn;
+  // split-K variant (conv_splitk.cu): a cluster of ks CTAs shares one output tile, CTA r takes the
+  // r-th contiguous range of the num_taps * kb_per_tap K blocks.  0 or 1: not split.
+  int ks;
   int m_tiles;
   int a_slice_dim, a_slice_step;
   int8_t tap_map[kMaxTaps];
@@ -59,5 +63,13 @@ inline int conv_tc_smem_bytes(int bk, int block_n, int stages) {
 }
 
 cudaError_t launch_conv_tc(const ConvTcParams& p, int num_sms, cudaStream_t stream);
+
+// Split-K variant: the fp32 staging area of the reduction (block_n x 128) aliases the operand ring.
+inline int conv_splitk_smem_bytes(int bk, int block_n, int stages) {
+  const int ring = stages * conv_tc_stage_bytes(bk, block_n);
+  const int staging = block_n * kTileM * 4;
+  return 1024 + (ring > staging ? ring : staging) + 256 + kMaxBlockN * 4;
+}
+cudaError_t launch_conv_splitk(const ConvTcParams& p, int num_sms, cudaStream_t stream);
 
 }  // namespace rnb

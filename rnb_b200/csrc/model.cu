@@ -346,8 +346,18 @@ bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
           (double)o.g.To * o.g.Ho * o.g.Wo * o.g.cout * (o.res_slot >= 0 ? 2 : 1);
   }
   if (name) *name = o.name;
-  if (kernel_kind)
-    *kernel_kind = dtype_ != RNB_DTYPE_BF16 ? 0 : (conv_patch_applicable(o.g) ? 2 : 1);
+  if (kernel_kind) {
+    // what the launch plan of the most recent batch size chose (before any forward: what applies)
+    int kind = dtype_ != RNB_DTYPE_BF16 ? 0 : (conv_patch_applicable(o.g) ? 2 : 1);
+    const auto it = plans_.find(last_batch_);
+    if (dtype_ == RNB_DTYPE_BF16 && it != plans_.end())
+      for (const Launch& l : it->second)
+        if (l.op == op) {
+          kind = l.patch ? 2 : (l.tc.ks > 1 ? 3 : 1);
+          break;
+        }
+    *kernel_kind = kind;
+  }
   if (flops_per_clip) *flops_per_clip = o.g.flops(1);
   if (act_bytes_per_clip) *act_bytes_per_clip = act * es;
   if (weight_bytes)
@@ -368,6 +378,7 @@ int R2P1DModel::profile(const void* in, int in_fmt, int batch, void* out, int ou
   std::vector<int> launch_op;
   if (dtype_ == RNB_DTYPE_BF16 && batch > 0 && batch <= max_batch_) {
     const std::vector<Launch>* plan = ensure_plan(batch, stream, err);
+    last_batch_ = batch;
     if (!plan) return RNB_ECUDA;
     for (const Launch& l : *plan) launch_op.push_back(l.op);
   } else {
@@ -425,7 +436,8 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
                         ? build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
                                                   &out->pp, &perr)
                         : build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
-                                               num_sms_, &out->tc, &perr, like->tc.cm, like->tc.cn);
+                                               num_sms_, &out->tc, &perr, like->tc.cm, like->tc.cn,
+                                               like->tc.ks, like->tc.block_n);
     return ok ? true : fail(perr);
   }
   // RNB_B200_PATCH_STREAM=0 keeps streamed-weight patch launches out of the candidate set
@@ -492,10 +504,45 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
       ok = true;
     }
   }
+  // split-K (conv_splitk.cu) where the tap kernel's grid leaves SMs idle or re-streams the
+  // operands of narrow channel tiles: clusters of 2-4 CTAs per output tile, wide or medium tiles.
+  // RNB_B200_SPLITK=0 keeps it out of the candidate set.
+  static const bool allow_splitk = [] {
+    const char* e = getenv("RNB_B200_SPLITK");
+    return !(e && e[0] == '0');
+  }();
+  if (allow_splitk && !failed && ok && !out->patch) {
+    static const int sk_cand[5][2] = {{2, 256}, {3, 256}, {2, 128}, {3, 128}, {4, 128}};
+    const int tap_items = out->tc.m_tiles * out->tc.n_tiles;
+    for (int ci = 0; ci < 5 && !failed; ++ci) {
+      ConvTcParams trial;
+      std::string serr;
+      if (!build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &trial,
+                                &serr, 0, 0, sk_cand[ci][0], sk_cand[ci][1]))
+        continue;  // e.g. fewer K blocks than CTAs
+      // only layers short of work items: more than ~3 waves of clusters is the tap kernel's domain
+      if (trial.m_tiles * trial.n_tiles * trial.ks > 3 * num_sms_ && tap_items > 2 * num_sms_)
+        continue;
+      float ms = 0.f;
+      if (!time_it([&] { return launch_conv_splitk(trial, num_sms_, stream); }, &ms)) {
+        failed = true;
+        break;
+      }
+      if (ms < best_ms * 0.97f) {
+        best_ms = ms;
+        out->patch = false;
+        out->tc = trial;
+      }
+    }
+  }
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   if (failed || !ok) return fail(perr.empty() ? "no launch candidate" : perr);
   return true;
+}
+
+cudaError_t R2P1DModel::launch_tc(const ConvTcParams& tc, cudaStream_t stream) const {
+  return tc.ks > 1 ? launch_conv_splitk(tc, num_sms_, stream) : launch_conv_tc(tc, num_sms_, stream);
 }
 
 // The flat launch list of one forward pass at `batch` clips.  Optionally (RNB_B200_CHUNK_MB > 0) a
@@ -594,6 +641,7 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
   const std::vector<Launch>* plan = nullptr;
   if (tc) {
     plan = ensure_plan(batch, stream, err);
+    last_batch_ = batch;
     if (!plan) return RNB_ECUDA;
   }
   cudaError_t e = cudaSuccess;
@@ -637,8 +685,8 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
   // ---- convolutions
   if (tc) {
     for (const Launch& l : *plan) {
-      const cudaError_t le = l.patch ? launch_conv_patch(l.pp, num_sms_, stream)
-                                     : launch_conv_tc(l.tc, num_sms_, stream);
+      const cudaError_t le =
+          l.patch ? launch_conv_patch(l.pp, num_sms_, stream) : launch_tc(l.tc, stream);
       if (!cuda_ok(le, ops_[l.op].name.c_str(), err)) return RNB_ECUDA;
       mark();
     }

@@ -85,7 +85,7 @@ class R2P1DModel {
   float* d_fc_w_ = nullptr;
   float* d_fc_b_ = nullptr;
   // One kernel launch of the tensor-core plan: convolution `op` over `batch` clips starting at clip
-  // `first`, through the patch kernel where it applies, else the tap kernel.
+  // `first`: the patch kernel (patch), else the tap kernel or its split-K variant (tc.ks > 1).
   struct Launch {
     int op = 0;
     int first = 0, batch = 0;
@@ -97,7 +97,9 @@ class R2P1DModel {
                  const Launch* like, Launch* out, std::string* err);
   bool build_plan(int batch, cudaStream_t stream, std::vector<Launch>* plan, std::string* err);
   const std::vector<Launch>* ensure_plan(int batch, cudaStream_t stream, std::string* err);
+  cudaError_t launch_tc(const ConvTcParams& tc, cudaStream_t stream) const;
   std::map<int, std::vector<Launch>> plans_;  // per batch size
+  int last_batch_ = 0;                        // batch size of the most recent forward
   int last_launches_ = 0;                     // kernels launched by the most recent forward
 };
 

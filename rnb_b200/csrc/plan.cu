@@ -156,7 +156,7 @@ struct View {
 bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                           const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                           const __nv_bfloat16* residual, bool relu, int num_sms, ConvTcParams* out,
-                          std::string* err, int force_cm, int force_cn) {
+                          std::string* err, int force_cm, int force_cn, int split_k, int split_n) {
   ConvTcParams& p = *out;
   memset(&p, 0, sizeof p);
   const int cp = g.cin_pad();
@@ -200,10 +200,24 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
     p.block_n = round_up(ceil_div(np, nt), 64);
     p.n_tiles = ceil_div(np, p.block_n);
   }
-  // small layers: more, narrower tiles until every SM has one
-  while (m_tiles * p.n_tiles < num_sms && p.block_n > 64) {
-    p.block_n = round_up(p.block_n, 64) - 64;
+  if (split_k > 1) {
+    // split-K (conv_splitk.cu): keep the channel tiles as wide as the accumulator allows -- the
+    // parallelism comes from K -- in near-equal multiples of 16 channels
+    const int cap = split_n >= 16 && split_n < kMaxBlockN ? split_n : kMaxBlockN;
+    const int nt = ceil_div(np, cap);
+    p.block_n = round_up(ceil_div(np, nt), 16);
     p.n_tiles = ceil_div(np, p.block_n);
+    const int total_kb = g.kt * g.kh * g.kw * p.kb_per_tap;  // upper bound; re-checked below
+    if (split_k > kMaxSplitK || split_k > total_kb) {
+      if (err) *err = "conv_tc: split-K factor too large";
+      return false;
+    }
+  } else {
+    // small layers: more, narrower tiles until every SM has one
+    while (m_tiles * p.n_tiles < num_sms && p.block_n > 64) {
+      p.block_n = round_up(p.block_n, 64) - 64;
+      p.n_tiles = ceil_div(np, p.block_n);
+    }
   }
   const int stage_bytes = conv_tc_stage_bytes(p.bk, p.block_n);
   int stages = (kSmemLimit - conv_tc_smem_bytes(p.bk, p.block_n, 0)) / stage_bytes;
@@ -250,6 +264,8 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
       }
     }
   }
+  if (split_k > 1) best_cm = best_cn = 1;
+  p.ks = split_k > 1 ? split_k : 0;
   p.cm = best_cm;
   p.cn = best_cn;
   p.a_slice_dim = sdim;
@@ -306,6 +322,14 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
         ++ntap;
       }
   p.num_taps = ntap;
+  if (p.ks > 1) {
+    const int total_kb = ntap * p.kb_per_tap;
+    const int per = ceil_div(total_kb, p.ks);
+    if ((p.ks - 1) * per >= total_kb) {
+      if (err) *err = "conv_tc: split-K factor leaves a CTA without K blocks";
+      return false;
+    }
+  }
   if (views.size() > 4) {
     if (err) *err = "conv_tc: more than four strided input views";
     return false;
