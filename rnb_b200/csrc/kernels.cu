@@ -2,7 +2,36 @@
 // All of them are HBM- or latency-bound byte movers: coalesced, vectorised, no tensor cores.
 #include "kernels.cuh"
 
+#include <stdio.h>
+
+#include <utility>
+
+#include "ptx.cuh"
+
 namespace rnb {
+
+namespace {
+// Launch with programmatic dependent launch allowed: the kernel may become resident while the
+// previous kernel in the stream drains (its prologue overlaps that tail; measured 0.9 us instead
+// of 4.1 us between kernels on a B200) and must execute griddepcontrol.wait before it touches
+// anything the previous kernel reads or writes.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                       Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+}  // namespace
+
 
 namespace {
 
@@ -89,10 +118,14 @@ to_stem_kernel(const In* __restrict__ in, int total_rows, Affine3 aff, uint4* __
                bool ncdhw) {
   __shared__ float px[kStemRows][kClipC][kStemPitch];
   const int row0 = blockIdx.x * kStemRows;
+  ptx::grid_dep_launch_dependents();
   for (int i = threadIdx.x; i < kStemRows * kClipC * 8; i += blockDim.x) {
     const int r = i / (kClipC * 8), c = (i / 8) % kClipC, m = i % 8;
     px[r][c][m < 4 ? m : kClipW + m] = 0.f;
   }
+  // (launched with programmatic dependent launch: the previous kernel in the stream may still be
+  // running, and the stem buffer this kernel overwrites may be one of its operands)
+  ptx::grid_dep_wait();
   // one thread loads 4 consecutive pixels of one (row, channel)
   for (int i = threadIdx.x; i < kStemRows * kClipC * (kClipW / 4); i += blockDim.x) {
     const int q = i % (kClipW / 4);
@@ -232,7 +265,7 @@ __device__ __forceinline__ void pool_fc_body(const In* __restrict__ x, int S, in
   const float inv = 1.f / (float)S;
   for (int c = 2 * threadIdx.x; c < C; c += 2 * blockDim.x) {
     float a0 = 0.f, a1 = 0.f;
-#pragma unroll 7
+#pragma unroll 16
     for (int s = 0; s < S; ++s) {
       if (sizeof(In) == 2) {
         const uint32_t u = *reinterpret_cast<const uint32_t*>(xb + (long long)s * C + c);
@@ -278,6 +311,8 @@ __global__ void __launch_bounds__(256)
 pool_fc_kernel(const In* __restrict__ x, int S, int C, const float* __restrict__ w,
                const float* __restrict__ bias, int num_classes, float* __restrict__ logits) {
   extern __shared__ float pooled[];
+  ptx::grid_dep_launch_dependents();
+  ptx::grid_dep_wait();  // (programmatic dependent launch: x is the previous kernel's output)
   pool_fc_body<In>(x, S, C, w, bias, num_classes, logits, nullptr, pooled);
 }
 
@@ -420,18 +455,16 @@ cudaError_t launch_pre_u8_to_stem(const uint8_t* in, int batch, const float* sca
                                   const float* bias3, __nv_bfloat16* out, cudaStream_t s) {
   const int rows = batch * kClipT * kClipH;
   if (rows == 0) return cudaSuccess;
-  to_stem_kernel<uint8_t><<<(rows + kStemRows - 1) / kStemRows, 256, 0, s>>>(
-      in, rows, make_affine(scale3, bias3), reinterpret_cast<uint4*>(out), false);
-  return cudaGetLastError();
+  return launch_pdl(to_stem_kernel<uint8_t>, dim3((rows + kStemRows - 1) / kStemRows), dim3(256), 0,
+                    s, in, rows, make_affine(scale3, bias3), reinterpret_cast<uint4*>(out), false);
 }
 
 cudaError_t launch_f32_ncdhw_to_stem(const float* in, int batch, __nv_bfloat16* out,
                                      cudaStream_t s) {
   const int rows = batch * kClipT * kClipH;
   if (rows == 0) return cudaSuccess;
-  to_stem_kernel<float><<<(rows + kStemRows - 1) / kStemRows, 256, 0, s>>>(
-      in, rows, make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
-  return cudaGetLastError();
+  return launch_pdl(to_stem_kernel<float>, dim3((rows + kStemRows - 1) / kStemRows), dim3(256), 0, s,
+                    in, rows, make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
 }
 
 cudaError_t launch_pre_u8_to_f32_ncdhw(const uint8_t* in, int batch, const float* scale3,
@@ -502,16 +535,14 @@ cudaError_t launch_pool_fc_bf16(const __nv_bfloat16* x, int B, int S, int C, con
                                 const float* bias, int num_classes, float* logits,
                                 cudaStream_t s) {
   if (B == 0) return cudaSuccess;
-  pool_fc_kernel<__nv_bfloat16><<<dim3(B, 10), 256, C * sizeof(float), s>>>(x, S, C, w, bias,
-                                                                          num_classes, logits);
-  return cudaGetLastError();
+  return launch_pdl(pool_fc_kernel<__nv_bfloat16>, dim3(B, 10), dim3(256), C * sizeof(float), s, x,
+                    S, C, w, bias, num_classes, logits);
 }
 cudaError_t launch_pool_fc_f32(const float* x, int B, int S, int C, const float* w,
                                const float* bias, int num_classes, float* logits, cudaStream_t s) {
   if (B == 0) return cudaSuccess;
-  pool_fc_kernel<float><<<dim3(B, 10), 256, C * sizeof(float), s>>>(x, S, C, w, bias, num_classes,
-                                                                  logits);
-  return cudaGetLastError();
+  return launch_pdl(pool_fc_kernel<float>, dim3(B, 10), dim3(256), C * sizeof(float), s, x, S, C, w,
+                    bias, num_classes, logits);
 }
 
 size_t pool_fc_classify_scratch_bytes(int batch, int num_classes) {
