@@ -355,7 +355,7 @@ def run_b200(args, rank, world, local_rank):
                      if (args.model, args.dtype, B, world) == ('r18', 'bf16', 16, 1) else None,
                      'traffic_unit': 'bytes',
                      'algorithmic_bytes_per_launch': sum(a * B + w for _, _, a, w, _ in info) / n_conv,
-                     'kernel': 'tcgen05 implicit-GEMM convolutions: conv_tc_kernel + conv_splitk_kernel + '
+                     'kernel': 'tcgen05 implicit-GEMM convolutions: conv_tc_kernel + conv_pair_kernel + conv_splitk_kernel + '
                                'conv_patch_kernel (%d launches per step)' % n_conv,
                      'by_kernel': by_kernel,
                      'peak_source': peak_src, 'frac_of_sustained': achieved / peak_sust,

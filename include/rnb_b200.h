@@ -103,7 +103,7 @@ int rnb_r2p1d_num_convs(void* handle);
  * activations in the handle's dtype; weights are per batch and reported separately), and which
  * kernel the launch plan of the most recent batch size runs it with (before the first forward: the
  * kernel that applies): 0 = fp32 direct convolution, 1 = conv_tc_kernel, 2 = conv_patch_kernel,
- * 3 = conv_splitk_kernel. */
+ * 3 = conv_splitk_kernel, 4 = conv_pair_kernel. */
 int rnb_r2p1d_profile(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
                       void* stream, float* ms, int cap);
 int rnb_r2p1d_op_info(void* handle, int op, char* name, int name_cap, double* flops_per_clip,

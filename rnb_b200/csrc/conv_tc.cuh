@@ -44,6 +44,9 @@ struct ConvTcParams {
   // split-K variant (conv_splitk.cu): a cluster of ks CTAs shares one output tile, CTA r takes the
   // r-th contiguous range of the num_taps * kb_per_tap K blocks.  0 or 1: not split.
   int ks;
+  // CTA-pair variant (conv_pair.cu): two CTAs on neighbouring position tiles share one channel tile,
+  // each loading half of it, one tcgen05.mma.cta_group::2 (M = 256).  0: not paired.
+  int pair;
   int m_tiles;
   int a_slice_dim, a_slice_step;
   int8_t tap_map[kMaxTaps];
@@ -71,5 +74,12 @@ inline int conv_splitk_smem_bytes(int bk, int block_n, int stages) {
   return 1024 + (ring > staging ? ring : staging) + 256 + kMaxBlockN * 4;
 }
 cudaError_t launch_conv_splitk(const ConvTcParams& p, int num_sms, cudaStream_t stream);
+
+// CTA-pair variant: a stage holds 128 activation rows and HALF of the weight tile.
+inline int conv_pair_stage_bytes(int bk, int block_n) { return (kTileM + block_n / 2) * bk * 2; }
+inline int conv_pair_smem_bytes(int bk, int block_n, int stages) {
+  return 1024 + stages * conv_pair_stage_bytes(bk, block_n) + 256 + kMaxBlockN * 4;
+}
+cudaError_t launch_conv_pair(const ConvTcParams& p, int num_sms, cudaStream_t stream);
 
 }  // namespace rnb

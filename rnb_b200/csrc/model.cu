@@ -353,7 +353,7 @@ bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
     if (dtype_ == RNB_DTYPE_BF16 && it != plans_.end())
       for (const Launch& l : it->second)
         if (l.op == op) {
-          kind = l.patch ? 2 : (l.tc.ks > 1 ? 3 : 1);
+          kind = l.patch ? 2 : (l.tc.pair ? 4 : (l.tc.ks > 1 ? 3 : 1));
           break;
         }
     *kernel_kind = kind;
@@ -437,7 +437,7 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
                                                   &out->pp, &perr)
                         : build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
                                                num_sms_, &out->tc, &perr, like->tc.cm, like->tc.cn,
-                                               like->tc.ks, like->tc.block_n);
+                                               like->tc.ks, like->tc.block_n, like->tc.pair);
     return ok ? true : fail(perr);
   }
   // RNB_B200_PATCH_STREAM=0 keeps streamed-weight patch launches out of the candidate set
@@ -535,6 +535,37 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
       }
     }
   }
+  // CTA pairs (conv_pair.cu): half the weight bytes per SM, the larger operand of the conv3-conv5
+  // layers; channel tiles of at most 256 / 192 / 128 / 64.  RNB_B200_PAIR=0 keeps them out.
+  static const bool allow_pair = [] {
+    const char* e = getenv("RNB_B200_PAIR");
+    return !(e && e[0] == '0');
+  }();
+  if (allow_pair && !failed && ok) {
+    int seen[4] = {0, 0, 0, 0};
+    static const int caps[4] = {256, 192, 128, 64};
+    for (int ci = 0; ci < 4 && !failed; ++ci) {
+      ConvTcParams trial;
+      std::string serr;
+      if (!build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &trial,
+                                &serr, 0, 0, 0, caps[ci], 1))
+        continue;  // e.g. a single position tile
+      bool dup = false;
+      for (int k = 0; k < ci; ++k) dup = dup || seen[k] == trial.block_n;
+      seen[ci] = trial.block_n;
+      if (dup) continue;
+      float ms = 0.f;
+      if (!time_it([&] { return launch_conv_pair(trial, num_sms_, stream); }, &ms)) {
+        failed = true;
+        break;
+      }
+      if (ms < best_ms * 0.97f) {
+        best_ms = ms;
+        out->patch = false;
+        out->tc = trial;
+      }
+    }
+  }
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   if (failed || !ok) return fail(perr.empty() ? "no launch candidate" : perr);
@@ -542,6 +573,7 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
 }
 
 cudaError_t R2P1DModel::launch_tc(const ConvTcParams& tc, cudaStream_t stream) const {
+  if (tc.pair) return launch_conv_pair(tc, num_sms_, stream);
   return tc.ks > 1 ? launch_conv_splitk(tc, num_sms_, stream) : launch_conv_tc(tc, num_sms_, stream);
 }
 

@@ -85,7 +85,8 @@ class R2P1DModel {
   float* d_fc_w_ = nullptr;
   float* d_fc_b_ = nullptr;
   // One kernel launch of the tensor-core plan: convolution `op` over `batch` clips starting at clip
-  // `first`: the patch kernel (patch), else the tap kernel or its split-K variant (tc.ks > 1).
+  // `first`: the patch kernel (patch), else the tap kernel, its CTA-pair variant (tc.pair) or its
+  // split-K variant (tc.ks > 1).
   struct Launch {
     int op = 0;
     int first = 0, batch = 0;

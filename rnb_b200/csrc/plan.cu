@@ -156,7 +156,8 @@ struct View {
 bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                           const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                           const __nv_bfloat16* residual, bool relu, int num_sms, ConvTcParams* out,
-                          std::string* err, int force_cm, int force_cn, int split_k, int split_n) {
+                          std::string* err, int force_cm, int force_cn, int split_k, int split_n,
+                          int pair) {
   ConvTcParams& p = *out;
   memset(&p, 0, sizeof p);
   const int cp = g.cin_pad();
@@ -200,15 +201,20 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
     p.block_n = round_up(ceil_div(np, nt), 64);
     p.n_tiles = ceil_div(np, p.block_n);
   }
-  if (split_k > 1) {
+  if (pair && (split_k > 1 || m_tiles < 2)) {
+    if (err) *err = "conv_tc: CTA pairs need two position tiles and exclude split-K";
+    return false;
+  }
+  if (split_k > 1 || pair) {
     // split-K (conv_splitk.cu): keep the channel tiles as wide as the accumulator allows -- the
-    // parallelism comes from K -- in near-equal multiples of 16 channels
+    // parallelism comes from K -- in near-equal multiples of 16 channels.  CTA pairs
+    // (conv_pair.cu): wide tiles too, each CTA holds half of one.
     const int cap = split_n >= 16 && split_n < kMaxBlockN ? split_n : kMaxBlockN;
     const int nt = ceil_div(np, cap);
     p.block_n = round_up(ceil_div(np, nt), 16);
     p.n_tiles = ceil_div(np, p.block_n);
     const int total_kb = g.kt * g.kh * g.kw * p.kb_per_tap;  // upper bound; re-checked below
-    if (split_k > kMaxSplitK || split_k > total_kb) {
+    if (split_k > 1 && (split_k > kMaxSplitK || split_k > total_kb)) {
       if (err) *err = "conv_tc: split-K factor too large";
       return false;
     }
@@ -219,7 +225,8 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
       p.n_tiles = ceil_div(np, p.block_n);
     }
   }
-  const int stage_bytes = conv_tc_stage_bytes(p.bk, p.block_n);
+  const int stage_bytes =
+      pair ? conv_pair_stage_bytes(p.bk, p.block_n) : conv_tc_stage_bytes(p.bk, p.block_n);
   int stages = (kSmemLimit - conv_tc_smem_bytes(p.bk, p.block_n, 0)) / stage_bytes;
   if (stages > 10) stages = 10;
   if (stages < 2) {
@@ -264,8 +271,9 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
       }
     }
   }
-  if (split_k > 1) best_cm = best_cn = 1;
+  if (split_k > 1 || pair) best_cm = best_cn = 1;
   p.ks = split_k > 1 ? split_k : 0;
+  p.pair = pair ? 1 : 0;
   p.cm = best_cm;
   p.cn = best_cn;
   p.a_slice_dim = sdim;
@@ -359,7 +367,8 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   {
     const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)np};
     const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
-    const uint32_t box[2] = {(uint32_t)p.bk, (uint32_t)(p.block_n / p.cm)};
+    // rows one CTA fetches: its share of a multicast tile, or its half of a CTA pair's tile
+    const uint32_t box[2] = {(uint32_t)p.bk, (uint32_t)(p.pair ? p.block_n / 2 : p.block_n / p.cm)};
     if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, swz, err)) return false;
   }
   p.y = y;

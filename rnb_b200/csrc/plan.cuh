@@ -52,9 +52,10 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                           const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                           const __nv_bfloat16* residual, bool relu, int num_sms, ConvTcParams* out,
                           std::string* err, int force_cm = 0, int force_cn = 0, int split_k = 0,
-                          int split_n = 0);
+                          int split_n = 0, int pair = 0);
 // (split_k > 1 plans the split-K variant, conv_splitk.cu: a cluster of split_k CTAs per output tile;
-// split_n caps its channel tile, default = the accumulator width)
+// split_n caps its channel tile, default = the accumulator width; pair = 1 plans the CTA-pair
+// variant, conv_pair.cu, whose channel tile split_n caps as well)
 
 // Patch kernel (conv_patch.cuh): stride-1 1x3x3 and 3x1x1 convolutions; weights resident in shared
 // memory when they fit next to two activation patches, streamed otherwise.  pair = 1 plans the

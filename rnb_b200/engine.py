@@ -182,7 +182,7 @@ class R2P1DEngine:
 
     def op_info(self):
         """[(state_dict prefix, FLOPs per clip, activation bytes per clip, weight bytes, kernel)]
-        per convolution; kernel is 'conv_ref', 'conv_tc', 'conv_patch' or 'conv_splitk' (what the
+        per convolution; kernel is 'conv_ref', 'conv_tc', 'conv_patch', 'conv_splitk' or 'conv_pair' (what the
         launch plan of the most recent batch size chose)."""
         info = []
         for i in range(self.num_convs):
@@ -192,7 +192,7 @@ class R2P1DEngine:
                                                   ctypes.byref(a), ctypes.byref(w),
                                                   ctypes.byref(k)))
             info.append((name.value.decode(), f.value, a.value, w.value,
-                         ('conv_ref', 'conv_tc', 'conv_patch', 'conv_splitk')[k.value]))
+                         ('conv_ref', 'conv_tc', 'conv_patch', 'conv_splitk', 'conv_pair')[k.value]))
         return info
 
     def profile(self, x):
