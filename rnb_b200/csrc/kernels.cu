@@ -167,7 +167,10 @@ to_stem_kernel(const In* __restrict__ in, int total_rows, Affine3 aff, uint4* __
     q.y = pack2(px[r][2][w0], 0.f);
     q.z = second ? pack2(px[r][0][w0 + 1], px[r][1][w0 + 1]) : 0u;
     q.w = second ? pack2(px[r][2][w0 + 1], 0.f) : 0u;
-    out[(long long)row * kChunksPerRow + o] = q;
+    // double-row layout: (b, t, h / 2, wo) x [row parity][4 chunks of 16 bytes]
+    const long long bt = row / kClipH;
+    const int h = row % kClipH;
+    out[(((bt * (kClipH / 2) + (h >> 1)) * (kClipW / 2) + wo) * 2 + (h & 1)) * 4 + cp] = q;
   }
 }
 

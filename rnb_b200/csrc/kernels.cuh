@@ -8,10 +8,11 @@
 namespace rnb {
 
 // ---- geometry of the stem input as the tcgen05 path wants it --------------------------------
-// "Unfolded" stem rows: for every (b, t, h, wo) the 8 input columns 2*wo-3 .. 2*wo+4 times 4
-// channel slots (rgb + one zero) are stored contiguously = 32 bf16 = 64 bytes, so that one filter
-// row of the 7x7 stride-2 stem becomes a K=32 slice of an implicit GEMM (column 8 and channel 4
-// carry zero weights).
+// "Unfolded double rows": for every (b, t, h2, wo) the 8 input columns 2*wo-3 .. 2*wo+4 times 4
+// channel slots (rgb + one zero) of input row 2*h2, then the same of input row 2*h2+1: 2 x 32 bf16
+// = 128 bytes.  The 7x7 stride-2 stem then is a stride-1 convolution over (h2, wo) with four
+// vertical taps (row pairs ho-2 .. ho+1) of K = 64 each (window column 8, channel slot 4 and the
+// upper row of the first pair carry zero weights) -- a shape the patch kernel runs.
 constexpr int kStemUnfold = 32;
 constexpr int kClipT = 8, kClipH = 112, kClipW = 112, kClipC = 3;
 

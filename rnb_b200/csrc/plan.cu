@@ -39,7 +39,12 @@ void pack_conv_weights_tc(const ConvGeom& g, const float* w, const float* scale,
             const float v = w[((((size_t)n * g.cin + c) * g.kt + dt) * g.kh + dh) * g.kw + dw];
             size_t k;
             if (g.stem_unfolded) {
-              k = (size_t)dh * cp + dw * 4 + c;  // filter row -> tap; (column, channel) -> K
+              // filter row dh reads input row 2*ho + dh - 3 = 2*(ho + j - 2) + par: row pair -> tap,
+              // (row of the pair, column, channel) -> K
+              const int off = dh - 3;
+              const int par = ((off % 2) + 2) % 2;
+              const int j = (off - par) / 2 + 2;
+              k = (size_t)j * cp + par * 32 + dw * 4 + c;
             } else {
               k = (size_t)((dt * g.kh + dh) * g.kw + dw) * cp + c;
             }
@@ -175,7 +180,11 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   p.residual = residual;
   p.relu = relu ? 1 : 0;
   p.cin_pad = cp;
-  p.bk = g.stem_unfolded ? 32 : 64;
+  if (g.stem_unfolded) {
+    if (err) *err = "conv_tc: the unfolded stem runs through the patch kernel";
+    return false;
+  }
+  p.bk = 64;
   p.kb_per_tap = ceil_div(cp, p.bk);
   p.Wo = g.Wo;
   p.Ho = g.Ho;
@@ -308,10 +317,10 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   int ntap = 0, tap_index = -1;
   for (int dt = 0; dt < g.kt; ++dt)
     for (int dh = 0; dh < g.kh; ++dh)
-      for (int dw = 0; dw < (g.stem_unfolded ? 1 : g.kw); ++dw) {
+      for (int dw = 0; dw < g.kw; ++dw) {
         ++tap_index;
         if (!tap_live(dt, g.pt, g.st, g.Ti, g.To) || !tap_live(dh, g.ph, g.sh, g.Hi, g.Ho) ||
-            (!g.stem_unfolded && !tap_live(dw, g.pw, g.sw, g.Wi, g.Wo)))
+            !tap_live(dw, g.pw, g.sw, g.Wi, g.Wo))
           continue;
         if (ntap >= kMaxTaps) {
           if (err) *err = "conv_tc: too many filter taps";
@@ -320,7 +329,7 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
         int pw = 0, ph = 0, pt = 0, sw_ = 0, sh_ = 0, st_ = 0;
         split(dt - g.pt, g.st, &pt, &st_);
         split(dh - g.ph, g.sh, &ph, &sh_);
-        if (!g.stem_unfolded) split(dw - g.pw, g.sw, &pw, &sw_);
+        split(dw - g.pw, g.sw, &pw, &sw_);
         p.tap_map[ntap] = (int8_t)view_index(pw, ph, pt);
         p.tap_dw[ntap] = (int8_t)sw_;
         p.tap_dh[ntap] = (int8_t)sh_;
@@ -346,9 +355,9 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   // ---- tensor maps
   const int swz = p.bk * 2;
   // input row pitch: the unfolded stem stores Wo groups of 32 per image row
-  const uint64_t in_w = g.stem_unfolded ? (uint64_t)g.Wo : (uint64_t)g.Wi;
+  const uint64_t in_w = (uint64_t)g.Wi;
   const uint64_t in_c = (uint64_t)cp;
-  const int eff_sw = g.stem_unfolded ? 1 : g.sw;
+  const int eff_sw = g.sw;
   for (size_t v = 0; v < views.size(); ++v) {
     const View& vw = views[v];
     const __nv_bfloat16* base =
@@ -395,11 +404,19 @@ int ilog2(int v) {
 PatchShape patch_shape(const ConvGeom& g, int pair) {
   const int ncta = pair ? 2 : 1;
   PatchShape s;
-  if (g.stem_unfolded || g.st != 1 || g.sh != 1 || g.sw != 1) return s;
+  if (!g.stem_unfolded && (g.st != 1 || g.sh != 1 || g.sw != 1)) return s;
   s.nkb = ceil_div(g.cin_pad(), 64);
   if (s.nkb > kPatchMaxKb) return s;
   const int np = g.cout_pad();
-  if (g.kt == 1 && g.kh == 3 && g.kw == 3 && g.ph == 1 && g.pw == 1 && g.pt == 0) {
+  if (g.stem_unfolded) {
+    // unfolded double rows: 8 output columns x 16 output rows per tile, three halo row pairs
+    // (two above, one below); a tap is an offset of one patch row pair = 8 rows
+    s.spatial = true;
+    s.taps = 4;
+    s.tw = 8; s.th = 16; s.tt = 1; s.lpw = 3; s.lph = 4;
+    s.pbw = 8; s.pbh = 16 + 3; s.pbt = 1;
+    s.eff = (double)g.Wo * g.Ho / ((double)ceil_div(g.Wo, 8) * ceil_div(g.Ho, 16) * 128);
+  } else if (g.kt == 1 && g.kh == 3 && g.kw == 3 && g.ph == 1 && g.pw == 1 && g.pt == 0) {
     // One frame per tile.  Accumulator rows use a power-of-two pitch that also holds the two halo
     // columns, so that a filter tap is a pure row offset (dh * pitch + dw) inside the patch.
     s.spatial = true;
@@ -520,18 +537,23 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   p.tiles_h = ceil_div(g.Ho, s.th);
   p.tiles_t = ceil_div(g.To, s.tt);
   p.tiles_b = B;
-  p.aw = s.spatial ? -1 : 0;
-  p.ah = s.spatial ? -1 : 0;
+  p.aw = g.stem_unfolded ? 0 : (s.spatial ? -1 : 0);
+  p.ah = g.stem_unfolded ? -2 : (s.spatial ? -1 : 0);
   p.at = s.spatial ? 0 : -1;
   p.Wo = g.Wo; p.Ho = g.Ho; p.To = g.To; p.B = B;
   p.cout_pad = np;
   p.relu = relu ? 1 : 0;
   for (int tap = 0; tap < s.taps; ++tap)
-    p.tap_shift[tap] = (int16_t)(s.spatial ? (tap / 3) * s.pbw + (tap % 3) : tap * s.pbw * s.pbh);
+    p.tap_shift[tap] = (int16_t)(g.stem_unfolded ? tap * s.pbw
+                                 : s.spatial    ? (tap / 3) * s.pbw + (tap % 3)
+                                                : tap * s.pbw * s.pbh);
   {
-    const uint64_t dims[5] = {(uint64_t)cp, (uint64_t)g.Wi, (uint64_t)g.Hi, (uint64_t)g.Ti, (uint64_t)B};
-    const uint64_t strides[4] = {(uint64_t)cp * 2, (uint64_t)g.Wi * cp * 2,
-                                 (uint64_t)g.Hi * g.Wi * cp * 2, (uint64_t)g.Ti * g.Hi * g.Wi * cp * 2};
+    // extent of the input the patches are cut from (the unfolded stem: Wo columns, Hi/2 row pairs)
+    const uint64_t in_w = g.stem_unfolded ? (uint64_t)g.Wo : (uint64_t)g.Wi;
+    const uint64_t in_h = g.stem_unfolded ? (uint64_t)(g.Hi / 2) : (uint64_t)g.Hi;
+    const uint64_t dims[5] = {(uint64_t)cp, in_w, in_h, (uint64_t)g.Ti, (uint64_t)B};
+    const uint64_t strides[4] = {(uint64_t)cp * 2, in_w * cp * 2, in_h * in_w * cp * 2,
+                                 (uint64_t)g.Ti * in_h * in_w * cp * 2};
     const uint32_t box[5] = {64u, (uint32_t)s.pbw, (uint32_t)s.pbh, (uint32_t)s.pbt, 1u};
     if (!encode_bf16(&p.a_map, x, 5, dims, strides, box, 128, err)) return false;
   }

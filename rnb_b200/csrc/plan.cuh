@@ -19,16 +19,19 @@ struct ConvGeom {
   int kt = 1, kh = 1, kw = 1;
   int st = 1, sh = 1, sw = 1;
   int pt = 0, ph = 0, pw = 0;
-  // stem: the input is the "unfolded" layout of kernels.cuh (B, Ti, Hi, Wo, 32) and only the
-  // filter rows remain as taps
+  // stem (7x7 stride 2 on 3 channels): the input is the "unfolded double-row" layout of
+  // kernels.cuh, (B, Ti, Hi/2, Wo, 64) -- per output column the 8 input columns x 4 channel slots it
+  // needs, of input rows 2*h2 and 2*h2+1 -- which turns the convolution into a stride-1 one with
+  // four vertical taps (row pairs h2 = ho-2 .. ho+1) of K = 64 for the patch kernel
   bool stem_unfolded = false;
 
-  int cin_pad() const { return stem_unfolded ? 32 : pad16(cin); }
+  int cin_pad() const { return stem_unfolded ? 64 : pad16(cin); }
   int cout_pad() const { return pad16(cout); }
-  int num_taps() const { return stem_unfolded ? kh : kt * kh * kw; }
+  int num_taps() const { return stem_unfolded ? 4 : kt * kh * kw; }
   int k_total() const { return num_taps() * cin_pad(); }
   long long in_elems(int B) const {
-    return stem_unfolded ? (long long)B * Ti * Hi * Wo * 32 : (long long)B * Ti * Hi * Wi * cin_pad();
+    return stem_unfolded ? (long long)B * Ti * (Hi / 2) * Wo * 64
+                         : (long long)B * Ti * Hi * Wi * cin_pad();
   }
   long long out_elems(int B) const { return (long long)B * To * Ho * Wo * cout_pad(); }
   double flops(int B) const {  // 2 x MACs, zero-pad taps counted, real channels only

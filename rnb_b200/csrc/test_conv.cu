@@ -451,13 +451,13 @@ static bool run_stem(int B) {
   rp.kt = 1; rp.kh = 7; rp.kw = 7; rp.st = 1; rp.sh = 2; rp.sw = 2; rp.pt = 0; rp.ph = 3; rp.pw = 3;
   rp.relu = 1;
   CK(launch_conv_ref(rp, 0));
-  ConvTcParams tp;
+  ConvPatchParams tp;
   std::string err;
-  if (!build_conv_tc_params(gu, B, du, dwp, dyb, dshift, nullptr, true, num_sms, &tp, &err)) {
+  if (!build_conv_patch_params(gu, B, du, dwp, dyb, dshift, nullptr, true, &tp, &err)) {
     printf("stem spatial PLAN FAILED: %s\n", err.c_str());
     return false;
   }
-  CK(launch_conv_tc(tp, num_sms, 0));
+  CK(launch_conv_patch(tp, num_sms, 0));
   CK(cudaDeviceSynchronize());
   std::vector<float> yr(out_pos * g.cout);
   std::vector<uint16_t> yb(out_pos * np);
@@ -479,9 +479,29 @@ static bool run_stem(int B) {
     }
   const double rel = max_err / (max_ref > 0 ? max_ref : 1);
   const bool pass = rel < 1e-2 && bad_pad == 0;
-  printf("%-28s B=%-2d N=%dx%d stages=%d taps=%d  max|ref|=%.3f max|err|=%.4f rel=%.2e pad_bad=%zu  %s\n",
-         "stem spatial (unfolded)", B, tp.n_tiles, tp.block_n, tp.num_stages, tp.num_taps, max_ref,
+  printf("%-28s B=%-2d N=%dx%d patch bufs=%d taps=%d  max|ref|=%.3f max|err|=%.4f rel=%.2e pad_bad=%zu  %s\n",
+         "stem spatial (unfolded)", B, tp.n_tiles, tp.block_n, tp.p_bufs, tp.num_taps, max_ref,
          max_err, rel, bad_pad, pass ? "PASS" : "FAIL");
+  if (pass && B >= 8) {
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    for (int i = 0; i < 3; ++i) CK(launch_conv_patch(tp, num_sms, 0));
+    CK(cudaEventRecord(e0));
+    for (int i = 0; i < 20; ++i) CK(launch_conv_patch(tp, num_sms, 0));
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    float ms;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    printf("    stem spatial perf: %.1f us  %.1f TFLOP/s\n", ms * 1e3 / 20,
+           g.flops(B) / (ms * 1e3 / 20) * 1e-6);
+    CK(cudaEventRecord(e0));
+    for (int i = 0; i < 20; ++i) CK(launch_pre_u8_to_stem(dframes, B, nullptr, nullptr, du, 0));
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    printf("    staging (uint8 -> unfolded rows) perf: %.1f us\n", ms * 1e3 / 20);
+  }
   cudaFree(dframes); cudaFree(dxf); cudaFree(dw); cudaFree(dscale); cudaFree(dshift); cudaFree(dy);
   cudaFree(du); cudaFree(dwp); cudaFree(dyb);
   return pass;
@@ -523,6 +543,7 @@ int main(int argc, char** argv) {
       c.B = perf_batch;
       run_case(c, 20);
     }
+    run_stem(perf_batch);
   }
   printf("%s (%d failed)\n", failed ? "SOME TESTS FAILED" : "ALL TESTS PASSED", failed);
   return failed ? 1 : 0;
