@@ -105,14 +105,21 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   constexpr int kNumCta = kPair ? 2 : 1;
   // one (tap, channel block) weight tile, or this CTA's half of it
   const uint32_t wtile_bytes = (p.block_n / kNumCta) * 128;
-  const uint32_t n_wtiles = p.num_taps * p.nkb;
-  const uint32_t n_wslots = kStream ? (uint32_t)p.b_stages : n_wtiles;
+  // tail block (resident single-CTA mode only): rows of tail_row bytes, swizzled at that width
+  const uint32_t tail_row = (!kStream && !kPair) ? (uint32_t)p.tail_ch * 2 : 0u;
+  const uint32_t wtail_bytes = p.block_n * tail_row;
+  const uint32_t wtap_bytes = p.nkb * wtile_bytes + wtail_bytes;  // all weight tiles of one tap
   const uint32_t pblock_bytes = p.patch_rows * 128;     // one channel block of a patch
-  const uint32_t patch_bytes = p.nkb * pblock_bytes;
+  const uint32_t ptail_off = p.nkb * pblock_bytes;      // the tail block follows the full ones
+  const uint32_t patch_bytes = ptail_off + p.patch_rows * tail_row;
   const uint32_t wbuf = smem_base;
-  const uint32_t pbuf = wbuf + n_wslots * wtile_bytes;
-  const uint32_t bars = pbuf + p.p_bufs * patch_bytes + 1024;  // +1024: rows past the last patch
-                                                               // that only garbage rows read
+  const uint32_t pbuf =
+      wbuf + (kStream ? (uint32_t)p.b_stages * wtile_bytes : (uint32_t)p.num_taps * wtap_bytes);
+  // +1024: rows past the last patch that only garbage rows read; then two residual tiles
+  const uint32_t rbuf = pbuf + p.p_bufs * patch_bytes + 1024;
+  const bool res_smem = kRes && !kStream && !kPair && p.res_smem;
+  const uint32_t rtile_bytes = res_smem ? (uint32_t)(p.n >> 6) * 16384u : 0u;
+  const uint32_t bars = rbuf + 2 * rtile_bytes;
   const uint32_t w_full = bars;
   const uint32_t p_full = bars + 8;                     // [kPatchMaxBufs]
   const uint32_t p_empty = p_full + 8 * kPatchMaxBufs;  // [kPatchMaxBufs]
@@ -122,6 +129,10 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   const uint32_t b_full = tmem_ptr_smem + 8;                  // [kPatchMaxBStages]
   const uint32_t b_empty = b_full + 8 * kPatchMaxBStages;     // [kPatchMaxBStages]
   static_assert(8 + 16 * kPatchMaxBufs + 32 + 8 + 16 * kPatchMaxBStages <= 256, "barrier area");
+  // resident mode uses the stream barriers for its taps (<= 12 with res_smem) and the last four
+  // for the residual tiles
+  const uint32_t res_full = b_empty + 8 * (kPatchMaxBStages - 4);   // [2]
+  const uint32_t res_empty = b_empty + 8 * (kPatchMaxBStages - 2);  // [2]
   const uint32_t shift_tab = bars + 256;
 
   const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_t * p.tiles_b;
@@ -136,6 +147,10 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.a_map);
     ptx::prefetch_tmap(&p.b_map);
+    if (tail_row) {
+      ptx::prefetch_tmap(&p.a_map_tail);
+      ptx::prefetch_tmap(&p.b_map_tail);
+    }
     ptx::mbar_init(w_full, 1);
     for (int s = 0; s < kPatchMaxBufs; ++s) {
       ptx::mbar_init(p_full + 8 * s, 1);
@@ -149,7 +164,8 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     }
     for (int s = 0; s < kPatchMaxBStages; ++s) {
       ptx::mbar_init(b_full + 8 * s, 1);
-      ptx::mbar_init(b_empty + 8 * s, 1);
+      // (the residual "empty" barriers take one arrival per epilogue warp)
+      ptx::mbar_init(b_empty + 8 * s, (res_smem && s >= kPatchMaxBStages - 2) ? kEpiThreads / 32 : 1);
     }
     ptx::fence_mbar_init();
   }
@@ -192,22 +208,26 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
       // tile starts on tap 0 while the other taps are still arriving, instead of idling for the
       // ~2 us the whole weight set takes at the SM's inbound TMA rate.
       const int row0 = rank * (p.n / kNumCta);
-      for (int tap = 0, i = 0; tap < p.num_taps; ++tap) {
-        if (rank == 0)
-          ptx::mbar_expect_tx_elect(b_full + 8 * tap, kNumCta * p.nkb * wtile_bytes);
-        for (int kb = 0; kb < p.nkb; ++kb, ++i) {
+      for (int tap = 0; tap < p.num_taps; ++tap) {
+        const uint32_t wt = wbuf + tap * wtap_bytes;
+        if (rank == 0) ptx::mbar_expect_tx_elect(b_full + 8 * tap, kNumCta * wtap_bytes);
+        for (int kb = 0; kb < p.nkb; ++kb) {
           if (kPair)
-            ptx::tma_load_2d_pair_elect(wbuf + i * wtile_bytes, &p.b_map, b_full_ld + 8 * tap,
+            ptx::tma_load_2d_pair_elect(wt + kb * wtile_bytes, &p.b_map, b_full_ld + 8 * tap,
                                         tap * p.cin_pad + kb * 64, row0);
           else
-            ptx::tma_load_2d_elect(wbuf + i * wtile_bytes, &p.b_map, b_full + 8 * tap,
+            ptx::tma_load_2d_elect(wt + kb * wtile_bytes, &p.b_map, b_full + 8 * tap,
                                    tap * p.cin_pad + kb * 64, 0);
         }
+        if (tail_row)
+          ptx::tma_load_2d_elect(wt + p.nkb * wtile_bytes, &p.b_map_tail, b_full + 8 * tap,
+                                 tap * p.cin_pad + p.nkb * 64, 0);
       }
     }
     ptx::grid_dep_wait();
     uint32_t pb = 0, ph = 0;
     uint32_t bs = 0, bphase = 0;
+    uint32_t rlocal = 0;
     for (int item = first_item; item < total_items; item += item_step) {
       const PatchItem tc = decode_patch_item(p, item, kNumCta, rank);
       // L2 prefetch of the patch `p.prefetch` items ahead: its real load can only be issued when a
@@ -236,6 +256,19 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
         else
           ptx::tma_load_5d_elect(dst, &p.a_map, p_full + 8 * pb, kb * 64, tc.w0 + p.aw,
                                  tc.h0 + p.ah, tc.t0 + p.at, tc.b);
+      }
+      if (tail_row)
+        ptx::tma_load_5d_elect(pbuf + pb * patch_bytes + ptail_off, &p.a_map_tail, p_full + 8 * pb,
+                               p.nkb * 64, tc.w0 + p.aw, tc.h0 + p.ah, tc.t0 + p.at, tc.b);
+      if (res_smem) {
+        // the residual rows of this item's output tile, into the tile buffer of its accumulator
+        const uint32_t acc = rlocal & 1, rphase = (rlocal >> 1) & 1;
+        ptx::mbar_wait(res_empty + 8 * acc, rphase ^ 1);
+        ptx::mbar_expect_tx_elect(res_full + 8 * acc, rtile_bytes);
+        for (int rb = 0; rb < (p.n >> 6); ++rb)
+          ptx::tma_load_5d_elect(rbuf + acc * rtile_bytes + rb * 16384, &p.r_map,
+                                 res_full + 8 * acc, rb * 64, tc.w0, tc.h0, tc.t0, tc.b);
+        ++rlocal;
       }
       if (kStream) {
         // my rows of the channel tile: the MMA takes columns [0, N/2) from the leader's shared
@@ -343,6 +376,16 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
               wt += wtile_bytes;
             }
           }
+          if (tail_row) {
+            // the trailing 16 / 32 channels: one / two K steps from the narrow-swizzle blocks
+            const uint64_t adesc = ptx::make_kmajor_desc(
+                pbuf + pb * patch_bytes + ptail_off + (uint32_t)p.tap_shift[tap] * tail_row, tail_row);
+            const uint64_t bdesc = ptx::make_kmajor_desc(wt, tail_row);
+            ptx::umma_bf16_elect(tmem_d, adesc, bdesc, idesc, accumulate);
+            if (tail_row > 32) ptx::umma_bf16_elect(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
+            accumulate = 1;
+            wt += wtail_bytes;
+          }
         }
         if (kPair) {
           ptx::umma_commit_pair_elect(p_empty + 8 * pb, 3);
@@ -409,7 +452,7 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
       Slice nxt2 = nxt;
       if (item + 2 * item_step < total_items) {
         nxt2 = slice_of(item + 2 * item_step);
-        if (kRes) prefetch_residual_l2(p.residual + nxt2.off, nxt2.ncols, nxt2.valid);
+        if (kRes && !res_smem) prefetch_residual_l2(p.residual + nxt2.off, nxt2.ncols, nxt2.valid);
       }
       if (kStream && cur.n0 != table_n0) {
         // shift table of this channel tile; the barriers order it against the previous readers
@@ -430,7 +473,14 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
                                  ,
                                  epi_cnt
 #endif
-      );
+                                 ,
+                                 res_smem ? rbuf + acc * rtile_bytes : 0u, row, res_full + 8 * acc,
+                                 acc_phase);
+      if (res_smem) {
+        // this warp has read its residual rows: the tile buffer may be refilled
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(res_empty + 8 * acc);
+      }
       // every TMEM read of this accumulator buffer has completed: hand it back, one arrival per
       // warp (hundreds of arrivals per tile on one mbarrier serialise)
       ptx::tc_fence_before();
@@ -448,11 +498,11 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     Slice cur = {}, nxt = {};
     if (first_item < total_items) {
       cur = slice_of(first_item);
-      if (kRes) prefetch_residual_l2(p.residual + cur.off, cur.ncols, cur.valid);
+      if (kRes && !res_smem) prefetch_residual_l2(p.residual + cur.off, cur.ncols, cur.valid);
     }
     if (first_item + item_step < total_items) {
       nxt = slice_of(first_item + item_step);
-      if (kRes) prefetch_residual_l2(p.residual + nxt.off, nxt.ncols, nxt.valid);
+      if (kRes && !res_smem) prefetch_residual_l2(p.residual + nxt.off, nxt.ncols, nxt.valid);
     }
     for (int item = first_item; item < total_items; item += item_step) {
       const Slice nxt2 = one_item(item, cur, nxt);
@@ -576,7 +626,8 @@ cudaError_t launch_conv_patch(const ConvPatchParams& p, int num_sms, cudaStream_
   const int ncta = p.pair ? 2 : 1;
   if (p.p_bufs < 2 || p.p_bufs > kPatchMaxBufs) return cudaErrorInvalidValue;
   const int smem = conv_patch_smem_bytes(p.nkb, p.patch_rows, p.num_taps, p.block_n / ncta,
-                                         p.b_stages, p.p_bufs);
+                                         p.b_stages, p.p_bufs, p.tail_ch,
+                                         (p.res_smem && p.residual) ? p.n / 64 : 0);
   if (p.pair)
     return p.b_stages > 0 ? launch_patch_mode<true, true>(p, num_sms, smem, stream)
                           : launch_patch_mode<false, true>(p, num_sms, smem, stream);

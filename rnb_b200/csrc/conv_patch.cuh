@@ -29,10 +29,20 @@ constexpr int kPatchMaxBufs = 4;    // activation patches in flight
 struct ConvPatchParams {
   alignas(64) CUtensorMap a_map;  // activation (C, W, H, T, B), box (64, pbox_w, pbox_h, pbox_t, 1)
   alignas(64) CUtensorMap b_map;  // packed weights (K_total, N), box (64, block_n)
+  // TAIL block (resident, non-pair mode): when cin_pad = 64 * nkb + 16 or + 32, the trailing
+  // channels get a block of their own with 32- / 64-byte rows and swizzle instead of a zero-filled
+  // 128-byte one: a quarter / half of the shared memory and of the fill bandwidth of that block
+  alignas(64) CUtensorMap a_map_tail;  // box (tail_ch, pbox_w, pbox_h, pbox_t, 1)
+  alignas(64) CUtensorMap b_map_tail;  // box (tail_ch, block_n)
+  // residual through shared memory (res_smem = 1; resident single-CTA mode, n = 64 or 128): the
+  // producer warp fetches the tile's residual rows by TMA a tile ahead, so that no global-memory
+  // latency sits in the epilogue between "accumulator full" and "accumulator free"
+  alignas(64) CUtensorMap r_map;       // residual (C, W, H, T, B), box (64, tile extents, 1)
   const float* shift;
   const __nv_bfloat16* residual;
   __nv_bfloat16* y;     // output (B, To, Ho, Wo, cout_pad): written with plain 32-byte stores
-  int nkb;              // 64-channel blocks of the input (cin_pad / 64 rounded up)
+  int nkb;              // full 64-channel blocks of the input (cin_pad / 64, rounded up if no tail)
+  int tail_ch;          // 0, or the 16 / 32 trailing channels held in the tail block
   int cin_pad;
   int patch_rows;       // rows (positions) of one patch block = pbox_w * pbox_h * pbox_t
   int num_taps;
@@ -44,6 +54,7 @@ struct ConvPatchParams {
 #ifdef RNB_PATCH_COUNTERS
   int dbg_launch;       // which of the 4 timestamp sets this launch writes
 #endif
+  int res_smem;
   int pair;             // 1: CTA pairs (cta_group::2), each CTA holds half of every weight tile
   // output tile: tw x th x tt positions, laid out in the accumulator with power-of-two pitches
   int tw, th, tt;
@@ -58,10 +69,12 @@ struct ConvPatchParams {
 
 // block_n here is the rows of a weight tile that ONE CTA holds (half the channel tile in pair mode)
 inline int conv_patch_smem_bytes(int nkb, int patch_rows, int num_taps, int block_n, int b_stages,
-                                 int p_bufs = 2) {
-  const int wtiles = b_stages > 0 ? b_stages : num_taps * nkb;
-  return 1024 + wtiles * block_n * 128 + p_bufs * nkb * patch_rows * 128 + 1024 /*slack rows*/ +
-         256 + kMaxBlockN * 4;
+                                 int p_bufs = 2, int tail_ch = 0, int res_blocks = 0) {
+  const int wbytes = b_stages > 0 ? b_stages * block_n * 128
+                                  : num_taps * block_n * (nkb * 128 + tail_ch * 2);
+  // (res_blocks: 64-channel blocks of a residual tile, two tiles in flight)
+  return 1024 + wbytes + p_bufs * patch_rows * (nkb * 128 + tail_ch * 2) + 1024 /*slack rows*/ +
+         2 * res_blocks * 16384 + 256 + kMaxBlockN * 4;
 }
 
 cudaError_t launch_conv_patch(const ConvPatchParams& p, int num_sms, cudaStream_t stream);

@@ -42,6 +42,19 @@ __device__ __forceinline__ void load_res16(const __nv_bfloat16* res_row, int col
     if (pred) ptx::ld_global_nc_v8(res_row + col, r);
   }
 }
+// Residual chunk c (16 channels) of accumulator row `row` from a TMA-written shared-memory tile:
+// blocks of 64 channels, [128 rows][128 bytes] each, 128-byte swizzle (16-byte unit u of row r sits
+// at unit u ^ (r & 7)).
+__device__ __forceinline__ void load_res16_smem(uint32_t res_tile, int row, int c, uint32_t (&r)[8]) {
+  const uint32_t base = res_tile + (uint32_t)(c >> 2) * 16384u + (uint32_t)row * 128u;
+  const uint32_t u0 = (uint32_t)(c & 3) * 2u, x = (uint32_t)row & 7u;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];\n"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(base + ((u0 ^ x) << 4)));
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];\n"
+               : "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(base + (((u0 + 1u) ^ x) << 4)));
+}
 template <bool kRes, bool kRelu>
 __device__ __forceinline__ void finish16(const uint32_t (&v)[16], const uint64_t (&sh)[8],
                                          const uint32_t (&r)[8], uint32_t (&o)[8]) {
@@ -83,16 +96,26 @@ __device__ __forceinline__ void epilogue_tile(uint32_t full_bar, uint32_t full_p
                                               ,
                                               unsigned long long (&epi_cnt)[6]
 #endif
-) {
+                                              ,
+                                              uint32_t res_tile = 0, int row = 0,
+                                              uint32_t res_bar = 0, uint32_t res_phase = 0) {
 #ifdef RNB_PATCH_COUNTERS
   long long epi_t = clock64();
 #endif
   uint32_t ra[8], rb[8];
-  epi::load_res16<kRes>(res_row, half * 16, valid && half < nchunk, ra);
-  epi::load_res16<kRes>(res_row, (half + 2) * 16, valid && half + 2 < nchunk, rb);
+  const bool res_smem = kRes && res_tile != 0;
+  if (!res_smem) {
+    epi::load_res16<kRes>(res_row, half * 16, valid && half < nchunk, ra);
+    epi::load_res16<kRes>(res_row, (half + 2) * 16, valid && half + 2 < nchunk, rb);
+  }
   EPI_MARK(0);
   ptx::mbar_wait(full_bar, full_phase);
   ptx::tc_fence_after();
+  if (res_smem) {
+    ptx::mbar_wait(res_bar, res_phase);
+    if (half < nchunk) epi::load_res16_smem(res_tile, row, half, ra);
+    if (half + 2 < nchunk) epi::load_res16_smem(res_tile, row, half + 2, rb);
+  }
   EPI_MARK(1);
   for (int c0 = half; c0 < nchunk; c0 += 4) {
     const int c1 = c0 + 2;
@@ -106,8 +129,13 @@ __device__ __forceinline__ void epilogue_tile(uint32_t full_bar, uint32_t full_p
     if (two) epi::load_shift16(shift_tab, c1 * 16, sb);
     // the residual rows of the next iteration, while this one converts
     uint32_t na[8], nb[8];
-    epi::load_res16<kRes>(res_row, (c0 + 4) * 16, valid && c0 + 4 < nchunk, na);
-    epi::load_res16<kRes>(res_row, (c1 + 4) * 16, valid && c1 + 4 < nchunk, nb);
+    if (res_smem) {
+      if (c0 + 4 < nchunk) epi::load_res16_smem(res_tile, row, c0 + 4, na);
+      if (c1 + 4 < nchunk) epi::load_res16_smem(res_tile, row, c1 + 4, nb);
+    } else {
+      epi::load_res16<kRes>(res_row, (c0 + 4) * 16, valid && c0 + 4 < nchunk, na);
+      epi::load_res16<kRes>(res_row, (c1 + 4) * 16, valid && c1 + 4 < nchunk, nb);
+    }
     EPI_MARK(2);
     ptx::tmem_ld_wait();
     EPI_MARK(3);

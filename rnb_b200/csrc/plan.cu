@@ -103,8 +103,9 @@ bool encode_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dim
     estr[i] = 1;
   }
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides[i];
-  const CUtensorMapSwizzle swz =
-      swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  const CUtensorMapSwizzle swz = swizzle_bytes == 128  ? CU_TENSOR_MAP_SWIZZLE_128B
+                                 : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                       : CU_TENSOR_MAP_SWIZZLE_32B;
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base),
                   gdim, gstr, bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -392,6 +393,7 @@ struct PatchShape {
   int tw = 0, th = 0, tt = 0, lpw = 0, lph = 0;
   int pbw = 0, pbh = 0, pbt = 0;  // patch box extent
   int n_tiles = 1, block_n = 0, b_stages = 0, p_bufs = 2;
+  int tail_ch = 0;  // trailing 16 / 32 channels in a narrow block of their own (resident mode)
   double eff = 0;
 };
 
@@ -459,13 +461,21 @@ PatchShape patch_shape(const ConvGeom& g, int pair) {
   s.patch_rows = s.pbw * s.pbh * s.pbt;
   // weights resident if they fit next to two patches, otherwise streamed per channel tile
   // (resident mode signals each tap's weights on one of the 2 * kPatchMaxBStages stream barriers)
+  // A trailing 16 or 32 channels (conv2 temporal: 144 = 2 x 64 + 16, stem temporal: 96 = 64 + 32)
+  // go into a narrow tail block instead of a zero-filled 64-channel one (single-CTA mode only).
+  const int cp = g.cin_pad();
+  const int tail = (!pair && cp > 64 && (cp % 64 == 16 || cp % 64 == 32)) ? cp % 64 : 0;
+  const int nkb_res = tail ? cp / 64 : s.nkb;
   if (np <= kMaxBlockN && s.taps <= 2 * kPatchMaxBStages &&
-      conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np / ncta, 0) <= kSmemLimit) {
+      conv_patch_smem_bytes(nkb_res, s.patch_rows, s.taps, np / ncta, 0, 2, tail) <= kSmemLimit) {
+    s.nkb = nkb_res;
+    s.tail_ch = tail;
     s.n_tiles = 1;
     s.block_n = np;
     s.b_stages = 0;
     while (s.p_bufs < kPatchMaxBufs &&
-           conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np / ncta, 0, s.p_bufs + 1) <= kSmemLimit)
+           conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np / ncta, 0, s.p_bufs + 1, tail) <=
+               kSmemLimit)
       ++s.p_bufs;
     s.ok = true;
     return s;
@@ -514,6 +524,7 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   p.residual = residual;
   p.y = y;
   p.nkb = s.nkb;
+  p.tail_ch = s.tail_ch;
   p.cin_pad = cp;
   p.patch_rows = s.patch_rows;
   p.num_taps = s.taps;
@@ -556,12 +567,51 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                                  (uint64_t)g.Ti * in_h * in_w * cp * 2};
     const uint32_t box[5] = {64u, (uint32_t)s.pbw, (uint32_t)s.pbh, (uint32_t)s.pbt, 1u};
     if (!encode_bf16(&p.a_map, x, 5, dims, strides, box, 128, err)) return false;
+    p.a_map_tail = p.a_map;
+    if (s.tail_ch) {
+      const uint32_t tbox[5] = {(uint32_t)s.tail_ch, (uint32_t)s.pbw, (uint32_t)s.pbh,
+                                (uint32_t)s.pbt, 1u};
+      if (!encode_bf16(&p.a_map_tail, x, 5, dims, strides, tbox, s.tail_ch * 2, err)) return false;
+    }
   }
   {
     const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)np};
     const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
     const uint32_t box[2] = {64u, (uint32_t)(s.block_n / (pair ? 2 : 1))};
     if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, 128, err)) return false;
+    p.b_map_tail = p.b_map;
+    if (s.tail_ch) {
+      const uint32_t tbox[2] = {(uint32_t)s.tail_ch, (uint32_t)s.block_n};
+      if (!encode_bf16(&p.b_map_tail, w_packed, 2, dims, strides, tbox, s.tail_ch * 2, err))
+        return false;
+    }
+  }
+  // Residual through shared memory (resident single-CTA mode, 64 or 128 output channels): two
+  // TMA-fed tiles of 128 rows, laid out like the accumulator rows.  RNB_B200_RES_SMEM=0 disables.
+  p.r_map = p.a_map;
+  static const bool allow_res_smem = [] {
+    const char* e = getenv("RNB_B200_RES_SMEM");
+    return !(e && e[0] == '0');
+  }();
+  if (allow_res_smem && residual && !pair && s.b_stages == 0 && (np == 64 || np == 128) &&
+      s.taps <= 2 * kPatchMaxBStages - 4) {
+    int bufs = s.p_bufs;
+    while (bufs > 2 && conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np, 0, bufs, s.tail_ch,
+                                             np / 64) > kSmemLimit)
+      --bufs;
+    if (conv_patch_smem_bytes(s.nkb, s.patch_rows, s.taps, np, 0, bufs, s.tail_ch, np / 64) <=
+        kSmemLimit) {
+      const int rt = 128 >> (s.lpw + s.lph);
+      const uint64_t dims[5] = {(uint64_t)np, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)g.To,
+                                (uint64_t)B};
+      const uint64_t strides[4] = {(uint64_t)np * 2, (uint64_t)g.Wo * np * 2,
+                                   (uint64_t)g.Ho * g.Wo * np * 2,
+                                   (uint64_t)g.To * g.Ho * g.Wo * np * 2};
+      const uint32_t box[5] = {64u, 1u << s.lpw, 1u << s.lph, (uint32_t)rt, 1u};
+      if (!encode_bf16(&p.r_map, residual, 5, dims, strides, box, 128, err)) return false;
+      p.res_smem = 1;
+      p.p_bufs = bufs;
+    }
   }
   return true;
 }

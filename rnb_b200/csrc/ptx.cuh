@@ -377,11 +377,12 @@ __device__ __forceinline__ uint32_t cvt_bf16x2(uint64_t v) {
   return r;
 }
 
-// Shared-memory matrix descriptor, K-major operand, rows of `swizzle_bytes` (128 or 64) bytes,
+// Shared-memory matrix descriptor, K-major operand, rows of `swizzle_bytes` (128, 64 or 32) bytes,
 // 8-row swizzle atoms stacked every 8*swizzle_bytes (SBO).  LBO is unused for swizzled K-major
 // layouts and set to 1; bits 46-47 carry the sm_100 descriptor version.
 __device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t smem_addr, uint32_t swizzle_bytes) {
-  const uint64_t layout = (swizzle_bytes == 128) ? 2ull : 4ull;  // SWIZZLE_128B : SWIZZLE_64B
+  // SWIZZLE_128B : SWIZZLE_64B : SWIZZLE_32B
+  const uint64_t layout = swizzle_bytes == 128 ? 2ull : (swizzle_bytes == 64 ? 4ull : 6ull);
   const uint64_t sbo = (8ull * swizzle_bytes) >> 4;
   return (uint64_t)((smem_addr & 0x3ffff) >> 4) | (1ull << 16) | (sbo << 32) | (1ull << 46) |
          (layout << 61);

@@ -193,10 +193,11 @@ static bool run_case(const Case& c, int perf_iters) {
           if (!(e <= perr)) perr = e;
         }
       const bool ok = perr / (max_ref > 0 ? max_ref : 1) < 1e-2 && pbad == 0 && nanc == 0;
-      printf("    patch kernel%s (tile w%d h%d t%d, N=%dx%d, %s, %d patch bufs, %d B stages): "
+      printf("    patch kernel%s (tile w%d h%d t%d, N=%dx%d, %s, %d patch bufs, %d B stages, tail %d, res_smem %d): "
              "max|err|=%.4f pad_bad=%zu nan=%zu  %s\n",
              mode ? " CTA-PAIR" : "", pp.tw, pp.th, pp.tt, pp.n_tiles, pp.block_n,
-             pp.b_stages ? "streamed" : "resident", pp.p_bufs, pp.b_stages, perr, pbad, nanc,
+             pp.b_stages ? "streamed" : "resident", pp.p_bufs, pp.b_stages, pp.tail_ch, pp.res_smem, perr, pbad,
+             nanc,
              ok ? "PASS" : "FAIL");
       if ((ok || getenv("RNB_FORCE_PERF")) && perf_iters > 0) {
         cudaEvent_t e0, e1;
