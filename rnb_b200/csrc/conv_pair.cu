@@ -121,7 +121,7 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
         const void* amap = &p.a_map[p.tap_map[tap]];
         const int cw = tc.w0 + p.tap_dw[tap], ch = tc.h0 + p.tap_dh[tap], ct = tc.t0 + p.tap_dt[tap];
         const int coff = p.tap_coff[tap], koff = p.tap_koff[tap];
-        for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+        for (int kb = 0; kb < p.tap_nkb[tap]; ++kb) {
           ptx::mbar_wait(empty_bar + 8 * stage, phase ^ 1);
           const uint32_t fb = full_ld + 8 * stage;
           const uint32_t sa = smem_base + stage * stage_bytes;
@@ -152,13 +152,13 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
         ptx::tc_fence_after();
         uint32_t accumulate = 0;
         for (int tap = 0; tap < p.num_taps; ++tap) {
-          for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+          for (int kb = 0; kb < p.tap_nkb[tap]; ++kb) {
             ptx::mbar_wait(full_bar + 8 * stage, phase);
             ptx::tc_fence_after();
             const uint32_t sa = smem_base + stage * stage_bytes;
             const uint64_t adesc = ptx::make_kmajor_desc(sa, swz);
             const uint64_t bdesc = ptx::make_kmajor_desc(sa + a_bytes, swz);
-            const int ksteps = min(p.bk, p.cin_pad - kb * p.bk) >> 4;
+            const int ksteps = min(p.bk, p.tap_cin[tap] - kb * p.bk) >> 4;
             ptx::umma_bf16_pair_elect(tmem_d, adesc, bdesc, idesc, accumulate);
             if (ksteps > 1) ptx::umma_bf16_pair_elect(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
             if (ksteps > 2) ptx::umma_bf16_pair_elect(tmem_d, adesc + 4, bdesc + 4, idesc, 1);

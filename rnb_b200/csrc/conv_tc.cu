@@ -154,7 +154,7 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
         const int cb = tc.b0 + sl_b;
         const int coff = p.tap_coff[tap];
         const int koff = p.tap_koff[tap];
-        for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+        for (int kb = 0; kb < p.tap_nkb[tap]; ++kb) {
           // free in EVERY CTA my slices go to (their MMA warps all arrive here)
           ptx::mbar_wait(empty_bar + 8 * stage, phase ^ 1);
           const uint32_t fb = full_bar + 8 * stage;
@@ -195,13 +195,13 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
       ptx::tc_fence_after();
       uint32_t accumulate = 0;
       for (int tap = 0; tap < p.num_taps; ++tap) {
-        for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+        for (int kb = 0; kb < p.tap_nkb[tap]; ++kb) {
           ptx::mbar_wait(full_bar + 8 * stage, phase);
           ptx::tc_fence_after();
           const uint32_t sa = smem_base + stage * stage_bytes;
           const uint64_t adesc = ptx::make_kmajor_desc(sa, swz);
           const uint64_t bdesc = ptx::make_kmajor_desc(sa + a_bytes, swz);
-          const int ksteps = min(p.bk, p.cin_pad - kb * p.bk) >> 4;
+          const int ksteps = min(p.bk, p.tap_cin[tap] - kb * p.bk) >> 4;
           // advancing 16 bf16 = 32 bytes along K inside the swizzle span: +2 in the address field
           if (live) {
             ptx::umma_bf16_elect(tmem_d, adesc, bdesc, idesc, accumulate);

@@ -55,6 +55,10 @@ struct ConvTcParams {
   int8_t tap_dt[kMaxTaps];
   int16_t tap_coff[kMaxTaps];  // channel offset inside the activation view
   int32_t tap_koff[kMaxTaps];  // K offset inside the packed weights
+  // K extent of each tap: cin_pad channels in kb_per_tap blocks for the filter taps; a fused 1x1x1
+  // shortcut convolution is one more tap with its own (smaller) channel count and tensor view
+  int16_t tap_cin[kMaxTaps];
+  int8_t tap_nkb[kMaxTaps];
 };
 
 inline int conv_tc_stage_bytes(int bk, int block_n) { return (kTileM + block_n) * bk * 2; }

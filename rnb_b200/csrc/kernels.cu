@@ -253,23 +253,32 @@ __global__ void bsc_to_bcs_kernel(const In* __restrict__ in, int C, int S, int c
 }
 
 // ------------------------------------------------------------------------------ pool + FC
-// grid (B, class_chunks), 256 threads.  Pooling: thread t owns channel pair (2t, 2t+1) (+512, ...)
-// and sums the S positions with coalesced 4-byte (bf16) / 8-byte (fp32) loads, S loads in flight.
-// Classifier: each warp takes classes of the chunk, lanes stride the C weights with 16-byte loads,
-// shuffle reduction.
+// grid (B, class_chunks), kPoolThreads threads.  Latency is what this step costs (50 KB per clip
+// and 0.8 MB of weights), so every load of a phase is in flight at once.  Pooling: the threads form
+// blockDim / (C/2) position groups; a thread owns one channel pair and the positions of its group
+// (S = 49: at most 13, unrolled), partial sums meet in shared memory.  Classifier: one class per
+// warp and pass, lanes stride the C weights with 16-byte loads, shuffle reduction.
+constexpr int kPoolThreads = 1024;
+constexpr int kPoolClassesPerCta = kPoolThreads / 32;
+
 template <typename In>
 __device__ __forceinline__ void pool_fc_body(const In* __restrict__ x, int S, int C,
                                              const float* __restrict__ w,
                                              const float* __restrict__ bias, int num_classes,
                                              float* __restrict__ logits, float* __restrict__ logits2,
                                              float* pooled) {
+  // pooled: C floats, then groups * C floats of partial sums (dynamic shared memory)
   const int b = blockIdx.x;
   const In* xb = x + (long long)b * S * C;
   const float inv = 1.f / (float)S;
-  for (int c = 2 * threadIdx.x; c < C; c += 2 * blockDim.x) {
+  const int pairs = C / 2;
+  const int groups = max(1, (int)blockDim.x / pairs);
+  float* part = pooled + C;
+  for (int i = threadIdx.x; i < groups * pairs; i += blockDim.x) {
+    const int g = i / pairs, c = 2 * (i - g * pairs);
     float a0 = 0.f, a1 = 0.f;
-#pragma unroll 16
-    for (int s = 0; s < S; ++s) {
+#pragma unroll 13
+    for (int s = g; s < S; s += groups) {
       if (sizeof(In) == 2) {
         const uint32_t u = *reinterpret_cast<const uint32_t*>(xb + (long long)s * C + c);
         a0 += __uint_as_float(u << 16);
@@ -280,8 +289,14 @@ __device__ __forceinline__ void pool_fc_body(const In* __restrict__ x, int S, in
         a1 += f.y;
       }
     }
-    pooled[c] = a0 * inv;
-    pooled[c + 1] = a1 * inv;
+    part[g * C + c] = a0;
+    part[g * C + c + 1] = a1;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f;
+    for (int g = 0; g < groups; ++g) a += part[g * C + c];  // fixed order: deterministic
+    pooled[c] = a * inv;
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -291,6 +306,7 @@ __device__ __forceinline__ void pool_fc_body(const In* __restrict__ x, int S, in
   for (int j = j0 + warp; j < j1; j += nwarps) {
     const float4* wj = reinterpret_cast<const float4*>(w + (long long)j * C);
     float acc = 0.f;
+#pragma unroll 4
     for (int c4 = lane; c4 < C / 4; c4 += 32) {
       const float4 wv = __ldg(wj + c4);
       const float4 pv = *reinterpret_cast<const float4*>(pooled + 4 * c4);
@@ -309,8 +325,17 @@ __device__ __forceinline__ void pool_fc_body(const In* __restrict__ x, int S, in
   }
 }
 
+// shared memory of the two kernels below: pooled values + per-group partial sums
+static inline size_t pool_fc_smem_bytes(int C) {
+  const int groups = kPoolThreads / (C / 2) > 0 ? kPoolThreads / (C / 2) : 1;
+  return (size_t)(1 + groups) * C * sizeof(float);
+}
+static inline int pool_fc_chunks(int num_classes) {
+  return (num_classes + kPoolClassesPerCta - 1) / kPoolClassesPerCta;
+}
+
 template <typename In>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kPoolThreads)
 pool_fc_kernel(const In* __restrict__ x, int S, int C, const float* __restrict__ w,
                const float* __restrict__ bias, int num_classes, float* __restrict__ logits) {
   extern __shared__ float pooled[];
@@ -324,15 +349,15 @@ pool_fc_kernel(const In* __restrict__ x, int S, int C, const float* __restrict__
 // that draws the last ticket sums the clips in a fixed order (deterministic, unlike atomics on the
 // sums), picks the arg-max with numpy's lowest-index tie rule, and re-arms the counter.
 template <typename In>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kPoolThreads)
 pool_fc_classify_kernel(const In* __restrict__ x, int S, int C, const float* __restrict__ w,
                         const float* __restrict__ bias, int num_classes,
                         float* __restrict__ logits, float* __restrict__ sum, int* __restrict__ cls,
                         float* __restrict__ staged, unsigned int* __restrict__ counter) {
   extern __shared__ float pooled[];
   __shared__ unsigned int ticket;
-  __shared__ float best_v[8];
-  __shared__ int best_i[8];
+  __shared__ float best_v[kPoolThreads / 32];
+  __shared__ int best_i[kPoolThreads / 32];
   pool_fc_body<In>(x, S, C, w, bias, num_classes, staged, logits, pooled);
   __threadfence();
   __syncthreads();
@@ -538,14 +563,15 @@ cudaError_t launch_pool_fc_bf16(const __nv_bfloat16* x, int B, int S, int C, con
                                 const float* bias, int num_classes, float* logits,
                                 cudaStream_t s) {
   if (B == 0) return cudaSuccess;
-  return launch_pdl(pool_fc_kernel<__nv_bfloat16>, dim3(B, 10), dim3(256), C * sizeof(float), s, x,
-                    S, C, w, bias, num_classes, logits);
+  return launch_pdl(pool_fc_kernel<__nv_bfloat16>, dim3(B, pool_fc_chunks(num_classes)),
+                    dim3(kPoolThreads), pool_fc_smem_bytes(C), s, x, S, C, w, bias, num_classes,
+                    logits);
 }
 cudaError_t launch_pool_fc_f32(const float* x, int B, int S, int C, const float* w,
                                const float* bias, int num_classes, float* logits, cudaStream_t s) {
   if (B == 0) return cudaSuccess;
-  return launch_pdl(pool_fc_kernel<float>, dim3(B, 10), dim3(256), C * sizeof(float), s, x, S, C, w,
-                    bias, num_classes, logits);
+  return launch_pdl(pool_fc_kernel<float>, dim3(B, pool_fc_chunks(num_classes)), dim3(kPoolThreads),
+                    pool_fc_smem_bytes(C), s, x, S, C, w, bias, num_classes, logits);
 }
 
 size_t pool_fc_classify_scratch_bytes(int batch, int num_classes) {
@@ -561,7 +587,8 @@ cudaError_t launch_pool_fc_classify_bf16(const __nv_bfloat16* x, int B, int S, i
   if (e != cudaSuccess) return e;
   unsigned int* counter = static_cast<unsigned int*>(scratch);
   float* staged = reinterpret_cast<float*>(static_cast<char*>(scratch) + 256);
-  pool_fc_classify_kernel<__nv_bfloat16><<<dim3(B, 10), 256, C * sizeof(float), s>>>(
+  pool_fc_classify_kernel<__nv_bfloat16><<<dim3(B, pool_fc_chunks(num_classes)), kPoolThreads,
+                                           pool_fc_smem_bytes(C), s>>>(
       x, S, C, w, bias, num_classes, logits, sum, cls, staged, counter);
   return cudaGetLastError();
 }

@@ -48,6 +48,7 @@ R2P1DModel::R2P1DModel(std::vector<int> layer_sizes, int start_idx, int end_idx,
                               {128, 4, 28, 28}, {256, 2, 14, 14}};
   static const Dims kOut[6] = {{}, {64, 8, 56, 56}, {64, 8, 56, 56}, {128, 4, 28, 28},
                                {256, 2, 14, 14}, {512, 1, 7, 7}};
+  if (const char* e = getenv("RNB_B200_FUSE_SHORTCUT")) fuse_shortcut_ = e[0] != '0';
   in_dims_ = kIn[start_idx];
   out_dims_ = kOut[end_idx];
 }
@@ -217,6 +218,30 @@ bool R2P1DModel::build_ops(std::string* err) {
       if (!add_st_conv(bp + ".conv2", SLOT_R, nxt, d1, cout, 3, 3, 3, 1, 1, 1, 1, 1, 1, bp + ".bn2",
                        true, res, false, &d2, err))
         return false;
+      if (ds && dtype_ == RNB_DTYPE_BF16 && fuse_shortcut_) {
+        // relu(bn2(conv2(x)) + bn_ds(conv_ds(x))): the shortcut's 1x1x1 temporal convolution is
+        // linear in its input, so it becomes one more K slice of conv2's temporal GEMM (its own
+        // BatchNorm scale folded into its weight rows, the two shifts added) instead of a launch
+        // of its own plus a residual read.  Its input, the shortcut's spatial output, moves to a
+        // slot of its own because slot M is reused before conv2's temporal convolution runs.
+        const size_t n = ops_.size();  // [.. ds.sp, ds.tp, c1.sp, c1.tp, c2.sp, c2.tp]
+        ConvOp& ds_sp = ops_[n - 6];
+        ConvOp& ds_tp = ops_[n - 5];
+        ConvOp& c2_tp = ops_[n - 1];
+        ds_sp.out_slot = SLOT_D;
+        c2_tp.g.extra_cin = ds_tp.g.cin;
+        c2_tp.g.extra_st = ds_tp.g.st;
+        c2_tp.g.extra_Ti = ds_tp.g.Ti;
+        c2_tp.g.extra_pitch = chan_pad(ds_tp.g.cin);
+        c2_tp.g.extra_coff = 0;
+        c2_tp.extra_slot = SLOT_D;
+        c2_tp.w_extra = ds_tp.w;
+        c2_tp.scale_extra = ds_tp.scale;
+        for (size_t i = 0; i < c2_tp.shift.size(); ++i) c2_tp.shift[i] += ds_tp.shift[i];
+        c2_tp.res_slot = -1;
+        c2_tp.name += "+shortcut";
+        ops_.erase(ops_.begin() + (n - 5));
+      }
       d = d2;
       std::swap(cur, nxt);
     }
@@ -271,7 +296,9 @@ int R2P1DModel::finalize(std::string* err) {
               cuda_ok(cudaMemcpy(op.d_shift, sh.data(), np * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err);
     if (ok && dtype_ == RNB_DTYPE_BF16) {
       std::vector<uint16_t> packed;
-      pack_conv_weights_tc(op.g, op.w.data(), op.scale.data(), &packed);
+      pack_conv_weights_tc(op.g, op.w.data(), op.scale.data(), &packed,
+                           op.w_extra.empty() ? nullptr : op.w_extra.data(),
+                           op.scale_extra.empty() ? nullptr : op.scale_extra.data());
       ok = cuda_ok(cudaMalloc(&op.d_w, packed.size() * 2), "cudaMalloc(weights)", err) &&
            cuda_ok(cudaMemcpy(op.d_w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice),
                    "cudaMemcpy(weights)", err);
@@ -340,7 +367,8 @@ bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
   const double es = (double)elem_size();
   double act;
   if (dtype_ == RNB_DTYPE_BF16) {
-    act = (double)o.g.in_elems(1) + (double)o.g.out_elems(1) * (o.res_slot >= 0 ? 2 : 1);
+    act = (double)o.g.in_elems(1) + (double)o.g.out_elems(1) * (o.res_slot >= 0 ? 2 : 1) +
+          (double)o.g.To * o.g.Ho * o.g.Wo * o.g.extra_cin_pad();
   } else {
     act = (double)o.g.Ti * o.g.Hi * o.g.Wi * o.g.cin +
           (double)o.g.To * o.g.Ho * o.g.Wo * o.g.cout * (o.res_slot >= 0 ? 2 : 1);
@@ -422,6 +450,11 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
   __nv_bfloat16* y = (__nv_bfloat16*)slots_[op.out_slot] + out_off;
   const __nv_bfloat16* res =
       op.res_slot >= 0 ? (const __nv_bfloat16*)slots_[op.res_slot] + out_off : nullptr;
+  const __nv_bfloat16* xe =
+      op.extra_slot >= 0
+          ? (const __nv_bfloat16*)slots_[op.extra_slot] +
+                (size_t)first * op.g.extra_Ti * op.g.Ho * op.g.Wo * op.g.extra_pitch
+          : nullptr;
   out->op = op_index;
   out->first = first;
   out->batch = batch;
@@ -437,7 +470,7 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
                                                   &out->pp, &perr)
                         : build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
                                                num_sms_, &out->tc, &perr, like->tc.cm, like->tc.cn,
-                                               like->tc.ks, like->tc.block_n, like->tc.pair);
+                                               like->tc.ks, like->tc.block_n, like->tc.pair, xe);
     return ok ? true : fail(perr);
   }
   // RNB_B200_PATCH_STREAM=0 keeps streamed-weight patch launches out of the candidate set
@@ -486,7 +519,7 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
   for (int ci = 0; ci < 6 && !failed; ++ci) {
     ConvTcParams trial;
     if (!build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &trial,
-                              &perr, cand[ci][0], cand[ci][1])) {
+                              &perr, cand[ci][0], cand[ci][1], 0, 0, 0, xe)) {
       failed = true;
       break;
     }
@@ -518,7 +551,7 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
       ConvTcParams trial;
       std::string serr;
       if (!build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &trial,
-                                &serr, 0, 0, sk_cand[ci][0], sk_cand[ci][1]))
+                                &serr, 0, 0, sk_cand[ci][0], sk_cand[ci][1], 0, xe))
         continue;  // e.g. fewer K blocks than CTAs
       // only layers short of work items: more than ~3 waves of clusters is the tap kernel's domain
       if (trial.m_tiles * trial.n_tiles * trial.ks > 3 * num_sms_ && tap_items > 2 * num_sms_)
@@ -548,7 +581,7 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
       ConvTcParams trial;
       std::string serr;
       if (!build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &trial,
-                                &serr, 0, 0, 0, caps[ci], 1))
+                                &serr, 0, 0, 0, caps[ci], 1, xe))
         continue;  // e.g. a single position tile
       bool dup = false;
       for (int k = 0; k < ci; ++k) dup = dup || seen[k] == trial.block_n;

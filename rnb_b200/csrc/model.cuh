@@ -16,15 +16,20 @@ struct HostTensor {
 };
 
 // activation slots of the arena; every op reads one or two slots and writes a third
-enum Slot { SLOT_U = 0, SLOT_X, SLOT_M, SLOT_R, SLOT_S, SLOT_Y, NUM_SLOTS };
+// U stem input, X/Y block in/out, M intermediate of a factorised conv, R first conv output,
+// S shortcut output (fp32 mode), D shortcut intermediate (bf16 mode: the shortcut's temporal
+// convolution is fused into the block's last convolution and reads it from there)
+enum Slot { SLOT_U = 0, SLOT_X, SLOT_M, SLOT_R, SLOT_S, SLOT_Y, SLOT_D, NUM_SLOTS };
 
 struct ConvOp {
   std::string name;  // state_dict prefix of the Conv3d, for error messages
   ConvGeom g;
   int in_slot = 0, out_slot = 0, res_slot = -1;
+  int extra_slot = -1;  // second input of a fused shortcut tap (ConvGeom::extra_*)
   bool relu = false;
   std::vector<float> w;             // torch layout (cout, cin, kt, kh, kw)
   std::vector<float> scale, shift;  // folded BatchNorm + bias, length cout
+  std::vector<float> w_extra, scale_extra;  // fused shortcut convolution (cout, extra_cin)
   // device copies
   void* d_w = nullptr;  // bf16 K-major rows (tensor cores) or fp32 (kt,kh,kw,cin,cout)
   float* d_scale = nullptr;
@@ -79,6 +84,9 @@ class R2P1DModel {
   std::vector<ConvOp> ops_;
   Dims in_dims_{}, out_dims_{};  // logical activation dims at the range boundaries
   int final_slot_ = SLOT_X;
+  // bf16 mode: fold each downsample shortcut's temporal convolution into the block's last
+  // convolution (RNB_B200_FUSE_SHORTCUT=0 keeps it a launch of its own + a residual read)
+  bool fuse_shortcut_ = true;
   void* slots_[NUM_SLOTS] = {};
   size_t slot_elems_per_clip_[NUM_SLOTS] = {};
   void* d_classify_scratch_ = nullptr;  // staged logits + arrival counter of the fused classifier

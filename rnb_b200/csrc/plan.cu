@@ -25,7 +25,8 @@ float bf16_bits_to_f32(uint16_t b) {
 }
 
 void pack_conv_weights_tc(const ConvGeom& g, const float* w, const float* scale,
-                          std::vector<uint16_t>* packed) {
+                          std::vector<uint16_t>* packed, const float* w_extra,
+                          const float* scale_extra) {
   const int kp = g.k_total();
   const int cp = g.cin_pad();
   packed->assign((size_t)g.cout_pad() * kp, 0);
@@ -50,6 +51,12 @@ void pack_conv_weights_tc(const ConvGeom& g, const float* w, const float* scale,
             }
             row[k] = f32_to_bf16_bits(v * sc);
           }
+    if (g.extra_cin && w_extra) {
+      const float se = scale_extra ? scale_extra[n] : 1.f;
+      for (int c = 0; c < g.extra_cin; ++c)
+        row[(size_t)g.num_taps() * cp + c] =
+            f32_to_bf16_bits(w_extra[(size_t)n * g.extra_cin + c] * se);
+    }
   }
 }
 
@@ -163,7 +170,7 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                           const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                           const __nv_bfloat16* residual, bool relu, int num_sms, ConvTcParams* out,
                           std::string* err, int force_cm, int force_cn, int split_k, int split_n,
-                          int pair) {
+                          int pair, const __nv_bfloat16* x_extra) {
   ConvTcParams& p = *out;
   memset(&p, 0, sizeof p);
   const int cp = g.cin_pad();
@@ -210,6 +217,10 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
     const int nt = ceil_div(np, kMaxBlockN);
     p.block_n = round_up(ceil_div(np, nt), 64);
     p.n_tiles = ceil_div(np, p.block_n);
+  }
+  if (g.extra_cin && (split_k > 1 || !x_extra)) {
+    if (err) *err = "conv_tc: a fused shortcut tap needs its tensor and excludes split-K";
+    return false;
   }
   if (pair && (split_k > 1 || m_tiles < 2)) {
     if (err) *err = "conv_tc: CTA pairs need two position tiles and exclude split-K";
@@ -337,8 +348,26 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
         p.tap_dt[ntap] = (int8_t)st_;
         p.tap_coff[ntap] = 0;
         p.tap_koff[ntap] = tap_index * cp;
+        p.tap_cin[ntap] = (int16_t)cp;
+        p.tap_nkb[ntap] = (int8_t)p.kb_per_tap;
         ++ntap;
       }
+  int extra_view = -1;
+  if (g.extra_cin) {
+    // the fused shortcut convolution: one tap at the output position itself, from its own view
+    if (ntap >= kMaxTaps || views.size() >= 4) {
+      if (err) *err = "conv_tc: no room for the fused shortcut tap";
+      return false;
+    }
+    extra_view = (int)views.size();
+    p.tap_map[ntap] = (int8_t)extra_view;
+    p.tap_dw[ntap] = p.tap_dh[ntap] = p.tap_dt[ntap] = 0;
+    p.tap_coff[ntap] = (int16_t)g.extra_coff;
+    p.tap_koff[ntap] = g.num_taps() * cp;
+    p.tap_cin[ntap] = (int16_t)g.extra_cin_pad();
+    p.tap_nkb[ntap] = (int8_t)ceil_div(g.extra_cin_pad(), p.bk);
+    ++ntap;
+  }
   p.num_taps = ntap;
   if (p.ks > 1) {
     const int total_kb = ntap * p.kb_per_tap;
@@ -348,7 +377,7 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
       return false;
     }
   }
-  if (views.size() > 4) {
+  if (views.size() + (extra_view >= 0 ? 1 : 0) > 4) {
     if (err) *err = "conv_tc: more than four strided input views";
     return false;
   }
@@ -374,6 +403,18 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
     if (!encode_bf16(&p.a_map[v], base, 5, dims, strides, box, swz, err)) return false;
   }
   for (size_t v = views.size(); v < 4; ++v) p.a_map[v] = p.a_map[0];
+  if (extra_view >= 0) {
+    // (B, extra_Ti / extra_st, Ho, Wo, extra_pitch): every extra_st-th frame of the second tensor
+    const uint64_t pc = (uint64_t)g.extra_pitch;
+    const uint64_t dims[5] = {pc, (uint64_t)g.Wo, (uint64_t)g.Ho,
+                              (uint64_t)((g.extra_Ti + g.extra_st - 1) / g.extra_st), (uint64_t)B};
+    const uint64_t strides[4] = {pc * 2, (uint64_t)g.Wo * pc * 2,
+                                 (uint64_t)g.extra_st * g.Ho * g.Wo * pc * 2,
+                                 (uint64_t)g.extra_Ti * g.Ho * g.Wo * pc * 2};
+    uint32_t box[5] = {(uint32_t)p.bk, (uint32_t)bw, (uint32_t)bh, (uint32_t)bt, (uint32_t)bb};
+    box[1 + p.a_slice_dim] /= (uint32_t)p.cn;
+    if (!encode_bf16(&p.a_map[extra_view], x_extra, 5, dims, strides, box, swz, err)) return false;
+  }
   {
     const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)np};
     const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
@@ -406,6 +447,7 @@ int ilog2(int v) {
 PatchShape patch_shape(const ConvGeom& g, int pair) {
   const int ncta = pair ? 2 : 1;
   PatchShape s;
+  if (g.extra_cin) return s;  // fused shortcut taps: tap / CTA-pair kernel only
   if (!g.stem_unfolded && (g.st != 1 || g.sh != 1 || g.sw != 1)) return s;
   s.nkb = ceil_div(g.cin_pad(), 64);
   if (s.nkb > kPatchMaxKb) return s;

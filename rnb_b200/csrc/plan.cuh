@@ -25,24 +25,33 @@ struct ConvGeom {
   // four vertical taps (row pairs h2 = ho-2 .. ho+1) of K = 64 for the patch kernel
   bool stem_unfolded = false;
 
+  // Fused shortcut (K-concatenation): extra_cin > 0 appends ONE tap that reads extra_cin channels
+  // (from channel extra_coff on) of a second tensor (B, extra_Ti, Ho, Wo, extra_pitch) at frame
+  // extra_st * t -- the 1x1x1 temporal convolution of a downsample shortcut, whose result would
+  // otherwise be added as a residual.  Tap kernel and CTA-pair kernel only.
+  int extra_cin = 0, extra_st = 1, extra_Ti = 0, extra_pitch = 0, extra_coff = 0;
+
   int cin_pad() const { return stem_unfolded ? 64 : pad16(cin); }
   int cout_pad() const { return pad16(cout); }
   int num_taps() const { return stem_unfolded ? 4 : kt * kh * kw; }
-  int k_total() const { return num_taps() * cin_pad(); }
+  int extra_cin_pad() const { return extra_cin ? pad16(extra_cin) : 0; }
+  int k_total() const { return num_taps() * cin_pad() + extra_cin_pad(); }
   long long in_elems(int B) const {
     return stem_unfolded ? (long long)B * Ti * (Hi / 2) * Wo * 64
                          : (long long)B * Ti * Hi * Wi * cin_pad();
   }
   long long out_elems(int B) const { return (long long)B * To * Ho * Wo * cout_pad(); }
   double flops(int B) const {  // 2 x MACs, zero-pad taps counted, real channels only
-    return 2.0 * B * To * Ho * Wo * (double)cout * cin * kt * kh * kw;
+    return 2.0 * B * To * Ho * Wo * (double)cout * ((double)cin * kt * kh * kw + extra_cin);
   }
 };
 
 // torch weight (cout, cin, kt, kh, kw) fp32 -> K-major bf16 rows (cout_pad, k_total); row n is
 // multiplied by scale[n] (the folded BatchNorm scale) before rounding when `scale` is given
+// (w_extra (cout, extra_cin) / scale_extra: the fused shortcut convolution's weights and scale)
 void pack_conv_weights_tc(const ConvGeom& g, const float* w, const float* scale,
-                          std::vector<uint16_t>* packed);
+                          std::vector<uint16_t>* packed, const float* w_extra = nullptr,
+                          const float* scale_extra = nullptr);
 
 // torch weight (cout, cin, kt, kh, kw) -> (kt, kh, kw, cin, cout) fp32 for the direct convolution
 void pack_conv_weights_ref(const ConvGeom& g, const float* w, std::vector<float>* packed);
@@ -55,7 +64,7 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                           const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                           const __nv_bfloat16* residual, bool relu, int num_sms, ConvTcParams* out,
                           std::string* err, int force_cm = 0, int force_cn = 0, int split_k = 0,
-                          int split_n = 0, int pair = 0);
+                          int split_n = 0, int pair = 0, const __nv_bfloat16* x_extra = nullptr);
 // (split_k > 1 plans the split-K variant, conv_splitk.cu: a cluster of split_k CTAs per output tile;
 // split_n caps its channel tile, default = the accumulator width; pair = 1 plans the CTA-pair
 // variant, conv_pair.cu, whose channel tile split_n caps as well)
