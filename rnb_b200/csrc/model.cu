@@ -227,20 +227,42 @@ bool R2P1DModel::build_ops(std::string* err) {
         const size_t n = ops_.size();  // [.. ds.sp, ds.tp, c1.sp, c1.tp, c2.sp, c2.tp]
         ConvOp& ds_sp = ops_[n - 6];
         ConvOp& ds_tp = ops_[n - 5];
+        ConvOp& c1_sp = ops_[n - 4];
+        ConvOp& c1_tp = ops_[n - 3];
         ConvOp& c2_tp = ops_[n - 1];
-        ds_sp.out_slot = SLOT_D;
+        // The shortcut's 1x1x1 SPATIAL convolution (stride 1,2,2) reads exactly the input positions
+        // the centre tap of conv1's 1x3x3 (stride 1,2,2) reads, and both are followed by their own
+        // BatchNorm + ReLU: it becomes extra output channels of conv1's spatial GEMM (zero weights
+        // on the other eight taps).  The widened output lives in slot D; conv1's temporal
+        // convolution reads its first pad16(mid) channels, the fused tap below the rest.
+        const int mid1_pad = chan_pad(c1_sp.g.cout);
+        const int ds_pad = chan_pad(ds_sp.g.cout);
+        const int wide = mid1_pad + ds_pad;
+        c1_sp.g.ncat = ds_sp.g.cout;
+        c1_sp.w_ncat = ds_sp.w;
+        c1_sp.scale_ncat = ds_sp.scale;
+        c1_sp.scale.resize(wide, 0.f);
+        c1_sp.shift.resize(wide, 0.f);
+        for (int i = 0; i < ds_sp.g.cout; ++i) {
+          c1_sp.scale[mid1_pad + i] = ds_sp.scale[i];
+          c1_sp.shift[mid1_pad + i] = ds_sp.shift[i];
+        }
+        c1_sp.out_slot = SLOT_D;
+        c1_sp.name += "+shortcut";
+        c1_tp.in_slot = SLOT_D;
+        c1_tp.g.in_pitch = wide;
         c2_tp.g.extra_cin = ds_tp.g.cin;
         c2_tp.g.extra_st = ds_tp.g.st;
         c2_tp.g.extra_Ti = ds_tp.g.Ti;
-        c2_tp.g.extra_pitch = chan_pad(ds_tp.g.cin);
-        c2_tp.g.extra_coff = 0;
+        c2_tp.g.extra_pitch = wide;
+        c2_tp.g.extra_coff = mid1_pad;
         c2_tp.extra_slot = SLOT_D;
         c2_tp.w_extra = ds_tp.w;
         c2_tp.scale_extra = ds_tp.scale;
         for (size_t i = 0; i < c2_tp.shift.size(); ++i) c2_tp.shift[i] += ds_tp.shift[i];
         c2_tp.res_slot = -1;
         c2_tp.name += "+shortcut";
-        ops_.erase(ops_.begin() + (n - 5));
+        ops_.erase(ops_.begin() + (n - 6), ops_.begin() + (n - 4));
       }
       d = d2;
       std::swap(cur, nxt);
@@ -274,7 +296,8 @@ int R2P1DModel::finalize(std::string* err) {
     need(SLOT_X, (size_t)in_dims_.T * in_dims_.H * in_dims_.W * chan_pad(in_dims_.C));
   }
   for (const ConvOp& op : ops_)
-    need(op.out_slot, (size_t)op.g.To * op.g.Ho * op.g.Wo * chan_pad(op.g.cout));
+    need(op.out_slot, (size_t)op.g.To * op.g.Ho * op.g.Wo *
+                          (dtype_ == RNB_DTYPE_BF16 ? op.g.cout_pad() : op.g.cout));
   for (int s = 0; s < NUM_SLOTS; ++s) {
     if (!slot_elems_per_clip_[s]) continue;
     const size_t bytes = slot_elems_per_clip_[s] * (size_t)max_batch_ * elem_size();
@@ -286,7 +309,7 @@ int R2P1DModel::finalize(std::string* err) {
 
   // ---- parameters
   for (ConvOp& op : ops_) {
-    const int np = chan_pad(op.g.cout);
+    const int np = dtype_ == RNB_DTYPE_BF16 ? op.g.cout_pad() : op.g.cout;
     std::vector<float> sc(np, 0.f), sh(np, 0.f);
     memcpy(sc.data(), op.scale.data(), op.scale.size() * 4);
     memcpy(sh.data(), op.shift.data(), op.shift.size() * 4);
@@ -298,7 +321,9 @@ int R2P1DModel::finalize(std::string* err) {
       std::vector<uint16_t> packed;
       pack_conv_weights_tc(op.g, op.w.data(), op.scale.data(), &packed,
                            op.w_extra.empty() ? nullptr : op.w_extra.data(),
-                           op.scale_extra.empty() ? nullptr : op.scale_extra.data());
+                           op.scale_extra.empty() ? nullptr : op.scale_extra.data(),
+                           op.w_ncat.empty() ? nullptr : op.w_ncat.data(),
+                           op.scale_ncat.empty() ? nullptr : op.scale_ncat.data());
       ok = cuda_ok(cudaMalloc(&op.d_w, packed.size() * 2), "cudaMalloc(weights)", err) &&
            cuda_ok(cudaMemcpy(op.d_w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice),
                    "cudaMemcpy(weights)", err);

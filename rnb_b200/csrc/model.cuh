@@ -29,7 +29,8 @@ struct ConvOp {
   bool relu = false;
   std::vector<float> w;             // torch layout (cout, cin, kt, kh, kw)
   std::vector<float> scale, shift;  // folded BatchNorm + bias, length cout
-  std::vector<float> w_extra, scale_extra;  // fused shortcut convolution (cout, extra_cin)
+  std::vector<float> w_extra, scale_extra;  // K-concatenated shortcut convolution (cout, extra_cin)
+  std::vector<float> w_ncat, scale_ncat;    // N-concatenated shortcut convolution (ncat, cin)
   // device copies
   void* d_w = nullptr;  // bf16 K-major rows (tensor cores) or fp32 (kt,kh,kw,cin,cout)
   float* d_scale = nullptr;

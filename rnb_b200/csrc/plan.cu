@@ -26,7 +26,7 @@ float bf16_bits_to_f32(uint16_t b) {
 
 void pack_conv_weights_tc(const ConvGeom& g, const float* w, const float* scale,
                           std::vector<uint16_t>* packed, const float* w_extra,
-                          const float* scale_extra) {
+                          const float* scale_extra, const float* w_ncat, const float* scale_ncat) {
   const int kp = g.k_total();
   const int cp = g.cin_pad();
   packed->assign((size_t)g.cout_pad() * kp, 0);
@@ -56,6 +56,16 @@ void pack_conv_weights_tc(const ConvGeom& g, const float* w, const float* scale,
       for (int c = 0; c < g.extra_cin; ++c)
         row[(size_t)g.num_taps() * cp + c] =
             f32_to_bf16_bits(w_extra[(size_t)n * g.extra_cin + c] * se);
+    }
+  }
+  if (g.ncat && w_ncat) {
+    // rows pad16(cout) ..: non-zero only in the K slice of the tap at offset zero
+    const int centre = (g.pt * g.kh + g.ph) * g.kw + g.pw;
+    for (int n = 0; n < g.ncat; ++n) {
+      uint16_t* row = packed->data() + (size_t)(pad16(g.cout) + n) * kp;
+      const float sc = scale_ncat ? scale_ncat[n] : 1.f;
+      for (int c = 0; c < g.cin; ++c)
+        row[(size_t)centre * cp + c] = f32_to_bf16_bits(w_ncat[(size_t)n * g.cin + c] * sc);
     }
   }
 }
@@ -386,7 +396,7 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   const int swz = p.bk * 2;
   // input row pitch: the unfolded stem stores Wo groups of 32 per image row
   const uint64_t in_w = (uint64_t)g.Wi;
-  const uint64_t in_c = (uint64_t)cp;
+  const uint64_t in_c = (uint64_t)(g.in_pitch ? g.in_pitch : cp);  // memory pitch of a position
   const int eff_sw = g.sw;
   for (size_t v = 0; v < views.size(); ++v) {
     const View& vw = views[v];
@@ -447,7 +457,8 @@ int ilog2(int v) {
 PatchShape patch_shape(const ConvGeom& g, int pair) {
   const int ncta = pair ? 2 : 1;
   PatchShape s;
-  if (g.extra_cin) return s;  // fused shortcut taps: tap / CTA-pair kernel only
+  // fused shortcuts and channel-sliced inputs: tap / CTA-pair kernel only
+  if (g.extra_cin || g.ncat || (g.in_pitch && g.in_pitch != g.cin_pad())) return s;
   if (!g.stem_unfolded && (g.st != 1 || g.sh != 1 || g.sw != 1)) return s;
   s.nkb = ceil_div(g.cin_pad(), 64);
   if (s.nkb > kPatchMaxKb) return s;

@@ -30,28 +30,39 @@ struct ConvGeom {
   // extra_st * t -- the 1x1x1 temporal convolution of a downsample shortcut, whose result would
   // otherwise be added as a residual.  Tap kernel and CTA-pair kernel only.
   int extra_cin = 0, extra_st = 1, extra_Ti = 0, extra_pitch = 0, extra_coff = 0;
+  // Fused shortcut (N-concatenation): ncat > 0 appends ncat output channels, from column
+  // pad16(cout) on, that see only the filter tap at offset zero (dt = pt, dh = ph, dw = pw) -- the
+  // 1x1x1 spatial convolution of a downsample shortcut, which reads exactly the positions that tap
+  // of the block's first (equally strided) convolution reads.  Tap / CTA-pair kernel only.
+  int ncat = 0;
+  // channels per position of the INPUT tensor in memory when it is a slice of a wider tensor
+  // (0: cin_pad())
+  int in_pitch = 0;
 
   int cin_pad() const { return stem_unfolded ? 64 : pad16(cin); }
-  int cout_pad() const { return pad16(cout); }
+  int cout_pad() const { return pad16(cout) + (ncat ? pad16(ncat) : 0); }
   int num_taps() const { return stem_unfolded ? 4 : kt * kh * kw; }
   int extra_cin_pad() const { return extra_cin ? pad16(extra_cin) : 0; }
   int k_total() const { return num_taps() * cin_pad() + extra_cin_pad(); }
   long long in_elems(int B) const {
     return stem_unfolded ? (long long)B * Ti * (Hi / 2) * Wo * 64
-                         : (long long)B * Ti * Hi * Wi * cin_pad();
+                         : (long long)B * Ti * Hi * Wi * (in_pitch ? in_pitch : cin_pad());
   }
   long long out_elems(int B) const { return (long long)B * To * Ho * Wo * cout_pad(); }
   double flops(int B) const {  // 2 x MACs, zero-pad taps counted, real channels only
-    return 2.0 * B * To * Ho * Wo * (double)cout * ((double)cin * kt * kh * kw + extra_cin);
+    return 2.0 * B * To * Ho * Wo *
+           ((double)cout * ((double)cin * kt * kh * kw + extra_cin) + (double)ncat * cin);
   }
 };
 
 // torch weight (cout, cin, kt, kh, kw) fp32 -> K-major bf16 rows (cout_pad, k_total); row n is
 // multiplied by scale[n] (the folded BatchNorm scale) before rounding when `scale` is given
-// (w_extra (cout, extra_cin) / scale_extra: the fused shortcut convolution's weights and scale)
+// (w_extra (cout, extra_cin) / scale_extra: the K-concatenated shortcut convolution's weights and
+// scale; w_ncat (ncat, cin) / scale_ncat: the N-concatenated one's)
 void pack_conv_weights_tc(const ConvGeom& g, const float* w, const float* scale,
                           std::vector<uint16_t>* packed, const float* w_extra = nullptr,
-                          const float* scale_extra = nullptr);
+                          const float* scale_extra = nullptr, const float* w_ncat = nullptr,
+                          const float* scale_ncat = nullptr);
 
 // torch weight (cout, cin, kt, kh, kw) -> (kt, kh, kw, cin, cout) fp32 for the direct convolution
 void pack_conv_weights_ref(const ConvGeom& g, const float* w, std::vector<float>* packed);
