@@ -26,7 +26,7 @@ LAYER_SIZES = {'r18': [2, 2, 2, 2, 2], 'r34': [2, 3, 4, 6, 3]}  # runner form: s
 GFLOP_PER_CLIP = {'r18': 42.172, 'r34': 76.853}
 METRIC = 'R(2+1)D clips/sec (8x112x112 clips)'
 CLIP_BYTES = 8 * 3 * 112 * 112
-NCU_DRAM_BYTES_PER_CONV_LAUNCH = 42.6e6  # profiles/r01_ncu_launches_v2.md (1705.6 MB / 40 launches)
+NCU_DRAM_BYTES_PER_CONV_LAUNCH = 50.6e6  # profiles/r01_ncu_launches_v3.md (1719.5 MB / 34 launches)
 FALLBACK_PEAK_TFLOPS = 1590.0  # /opt/skills/guides/B200_PROFILING.md, used only without MEASURED_PEAKS.json
 
 
@@ -348,8 +348,8 @@ def run_b200(args, rank, world, local_rank):
         'clocks': clocks,
         'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak_burst,
                      'unit': 'TFLOP/s', 'frac': achieved / peak_burst,
-                     # dram__bytes_read + write per convolution launch (average over the 40 launches
-                     # of one step), ncu capture in profiles/r01_ncu_launches_v2.md; only valid for
+                     # dram__bytes_read + write per convolution launch (average over the 34 launches
+                     # of one step), ncu capture in profiles/r01_ncu_launches_v3.md; only valid for
                      # the configuration that capture was taken on
                      'traffic': NCU_DRAM_BYTES_PER_CONV_LAUNCH
                      if (args.model, args.dtype, B, world) == ('r18', 'bf16', 16, 1) else None,

@@ -682,12 +682,90 @@ bool R2P1DModel::build_plan(int batch, cudaStream_t stream, std::vector<Launch>*
   return true;
 }
 
+// Plan cache (RNB_B200_PLAN_CACHE=<file>): the per-layer kernel choices of a batch size are appended
+// to the file after they have been timed, and reused -- without timing -- by any later process
+// whose model and batch size match.  Makes runs reproducible (the timing picks can differ between
+// near-equal candidates) and lets a profiler run use the plan of an unprofiled one.
+namespace {
+uint64_t fnv1a(uint64_t h, const void* data, size_t n) {
+  const unsigned char* p = static_cast<const unsigned char*>(data);
+  for (size_t i = 0; i < n; ++i) h = (h ^ p[i]) * 1099511628211ull;
+  return h;
+}
+}  // namespace
+
+uint64_t R2P1DModel::plan_key(int batch) const {
+  uint64_t h = 1469598103934665603ull;
+  h = fnv1a(h, &batch, sizeof batch);
+  h = fnv1a(h, &num_sms_, sizeof num_sms_);
+  for (const ConvOp& op : ops_) {
+    h = fnv1a(h, op.name.data(), op.name.size());
+    const int g[8] = {op.g.Ti, op.g.Hi, op.g.Wi, op.g.cin, op.g.cout, op.g.extra_cin, op.g.ncat,
+                      op.res_slot >= 0};
+    h = fnv1a(h, g, sizeof g);
+  }
+  return h;
+}
+
+bool R2P1DModel::load_cached_plan(const char* path, int batch, cudaStream_t stream,
+                                  std::vector<Launch>* plan) {
+  FILE* f = fopen(path, "r");
+  if (!f) return false;
+  const unsigned long long want = plan_key(batch);
+  char line[256];
+  bool found = false;
+  while (fgets(line, sizeof line, f)) {
+    unsigned long long key = 0;
+    int n = 0;
+    if (sscanf(line, "plan %llx %d", &key, &n) != 2 || key != want || n != (int)ops_.size()) continue;
+    found = true;
+    for (int i = 0; i < n && found; ++i) {
+      int op = -1, patch = 0, cm = 1, cn = 1, ks = 0, bn = 0, pair = 0;
+      if (!fgets(line, sizeof line, f) ||
+          sscanf(line, "%d %d %d %d %d %d %d", &op, &patch, &cm, &cn, &ks, &bn, &pair) != 7 ||
+          op != i) {
+        found = false;
+        break;
+      }
+      Launch like, l;
+      like.patch = patch != 0;
+      like.tc.cm = cm;
+      like.tc.cn = cn;
+      like.tc.ks = ks;
+      like.tc.block_n = bn;
+      like.tc.pair = pair;
+      std::string e;
+      if (!plan_conv(i, 0, batch, false, stream, &like, &l, &e)) found = false;
+      plan->push_back(l);
+    }
+    break;
+  }
+  fclose(f);
+  if (!found) plan->clear();
+  return found;
+}
+
+void R2P1DModel::save_cached_plan(const char* path, int batch, const std::vector<Launch>& plan) {
+  if (plan.size() != ops_.size()) return;  // chunked schedules are not cached
+  FILE* f = fopen(path, "a");
+  if (!f) return;
+  fprintf(f, "plan %llx %d\n", (unsigned long long)plan_key(batch), (int)plan.size());
+  for (const Launch& l : plan)
+    fprintf(f, "%d %d %d %d %d %d %d\n", l.op, l.patch ? 1 : 0, l.tc.cm, l.tc.cn, l.tc.ks,
+            l.tc.block_n, l.tc.pair);
+  fclose(f);
+}
+
 const std::vector<R2P1DModel::Launch>* R2P1DModel::ensure_plan(int batch, cudaStream_t stream,
                                                                std::string* err) {
   auto it = plans_.find(batch);
   if (it == plans_.end()) {
     std::vector<Launch> plan;
-    if (!build_plan(batch, stream, &plan, err)) return nullptr;
+    const char* cache = getenv("RNB_B200_PLAN_CACHE");
+    if (!(cache && cache[0] && load_cached_plan(cache, batch, stream, &plan))) {
+      if (!build_plan(batch, stream, &plan, err)) return nullptr;
+      if (cache && cache[0]) save_cached_plan(cache, batch, plan);
+    }
     it = plans_.emplace(batch, std::move(plan)).first;
   }
   return &it->second;

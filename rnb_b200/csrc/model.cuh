@@ -100,13 +100,16 @@ class R2P1DModel {
     int op = 0;
     int first = 0, batch = 0;
     bool patch = false;
-    ConvTcParams tc;
-    ConvPatchParams pp;
+    ConvTcParams tc = {};
+    ConvPatchParams pp = {};
   };
   bool plan_conv(int op_index, int first, int batch, bool chunked, cudaStream_t stream,
                  const Launch* like, Launch* out, std::string* err);
   bool build_plan(int batch, cudaStream_t stream, std::vector<Launch>* plan, std::string* err);
   const std::vector<Launch>* ensure_plan(int batch, cudaStream_t stream, std::string* err);
+  uint64_t plan_key(int batch) const;
+  bool load_cached_plan(const char* path, int batch, cudaStream_t stream, std::vector<Launch>* plan);
+  void save_cached_plan(const char* path, int batch, const std::vector<Launch>& plan);
   cudaError_t launch_tc(const ConvTcParams& tc, cudaStream_t stream) const;
   std::map<int, std::vector<Launch>> plans_;  // per batch size
   int last_batch_ = 0;                        // batch size of the most recent forward

@@ -436,3 +436,35 @@ def test_chunked_schedule_gives_identical_logits(lib, tmp_path):
     (y0, n0), (y1, n1) = outs
     assert n0 == 36 and n1 > 36
     assert torch.equal(y0, y1)
+
+
+def test_plan_cache_reproduces_the_plan(lib, tmp_path):
+    """RNB_B200_PLAN_CACHE: the first process times the candidates and appends its per-layer choices
+    to the file; a second process reuses them without timing and must produce bit-identical logits
+    (same kernels, same summation order) and report the same kernel per layer."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, torch; sys.path.insert(0, %r)\n"
+        "from rnb_b200.engine import R2P1DEngine, random_state_dict\n"
+        "eng = R2P1DEngine('cuda:0', random_state_dict(seed=7), max_batch=16)\n"
+        "g = torch.Generator().manual_seed(13)\n"
+        "x = torch.randint(0, 256, (16, 8, 3, 112, 112), dtype=torch.uint8, generator=g).cuda()\n"
+        "y = eng(x).cpu().clone(); torch.cuda.synchronize()\n"
+        "torch.save((y, [k for *_, k in eng.op_info()]), sys.argv[1])\n" % root)
+    cache = str(tmp_path / 'plan.txt')
+    env = dict(os.environ, RNB_B200_PLAN_CACHE=cache)
+    outs = []
+    for i in range(2):
+        path = str(tmp_path / ('run%d.pt' % i))
+        subprocess.run([sys.executable, '-c', code, path], check=True, env=env, timeout=600)
+        outs.append(torch.load(path))
+        if i == 0:
+            text = open(cache).read()
+            assert text.count('plan ') == 1
+    assert open(cache).read() == text      # the second run found its plan and appended nothing
+    (y0, k0), (y1, k1) = outs
+    assert k0 == k1
+    assert torch.equal(y0, y1)
