@@ -271,7 +271,7 @@ cudaError_t launch_pair_variant(const ConvTcParams& p, int num_sms, int smem, cu
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[3];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   attr[1].id = cudaLaunchAttributeClusterDimension;
@@ -295,6 +295,8 @@ cudaError_t launch_pair_variant(const ConvTcParams& p, int num_sms, int smem, cu
   }
   const int pairs = items < max_pairs ? items : max_pairs;
   cfg.gridDim = dim3(2 * pairs);
+  cfg.numAttrs = add_l2_output_window(attr, cfg.numAttrs, p.y,
+                                      (size_t)p.B * p.To * p.Ho * p.Wo * p.cout_pad * 2);
   return cudaLaunchKernelEx(&cfg, conv_pair_kernel<kRes, kRelu>, p);
 }
 }  // namespace

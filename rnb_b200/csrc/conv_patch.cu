@@ -582,7 +582,7 @@ cudaError_t launch_patch_variant(const ConvPatchParams& p, int num_sms, int smem
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[3];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
@@ -607,6 +607,8 @@ cudaError_t launch_patch_variant(const ConvPatchParams& p, int num_sms, int smem
   }
   const int groups = items < max_groups ? items : max_groups;
   cfg.gridDim = dim3(groups * ncta);
+  cfg.numAttrs = add_l2_output_window(attr, cfg.numAttrs, p.y,
+                                      (size_t)p.B * p.To * p.Ho * p.Wo * p.cout_pad * 2);
   return cudaLaunchKernelEx(&cfg, conv_patch_kernel<kRes, kRelu, kStream, kPair>, p);
 }
 

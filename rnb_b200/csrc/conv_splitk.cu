@@ -279,7 +279,7 @@ cudaError_t launch_sk_variant(const ConvTcParams& p, int num_sms, int smem, cuda
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[3];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   attr[1].id = cudaLaunchAttributeClusterDimension;
@@ -303,6 +303,8 @@ cudaError_t launch_sk_variant(const ConvTcParams& p, int num_sms, int smem, cuda
   }
   const int clusters = items < max_clusters ? items : max_clusters;
   cfg.gridDim = dim3(clusters * p.ks);
+  cfg.numAttrs = add_l2_output_window(attr, cfg.numAttrs, p.y,
+                                      (size_t)p.B * p.To * p.Ho * p.Wo * p.cout_pad * 2);
   return cudaLaunchKernelEx(&cfg, conv_splitk_kernel<kRes, kRelu>, p);
 }
 }  // namespace

@@ -12,6 +12,7 @@
 //               bias (shift; the scale lives in the weights), optional residual add and ReLU, bf16
 //               pack, one 32-byte global store per 16 channels (rows outside the tensor masked).
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "conv_tc.cuh"
 #include "epilogue.cuh"
@@ -345,7 +346,7 @@ cudaError_t launch_variant(const ConvTcParams& p, int num_sms, int smem, cudaStr
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[3];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
@@ -370,9 +371,51 @@ cudaError_t launch_variant(const ConvTcParams& p, int num_sms, int smem, cudaStr
   }
   const int clusters = items < max_clusters ? items : max_clusters;
   cfg.gridDim = dim3(clusters * csize);
+  cfg.numAttrs = add_l2_output_window(attr, cfg.numAttrs, p.y,
+                                      (size_t)p.B * p.To * p.Ho * p.Wo * p.cout_pad * 2);
   return cudaLaunchKernelEx(&cfg, conv_tc_kernel<kRes, kRelu>, p);
 }
 }  // namespace
+
+int add_l2_output_window(cudaLaunchAttribute* attr, int n, const void* ptr, size_t bytes) {
+  // carve-out size per device, set once (0 = feature off)
+  static size_t carve[64] = {};
+  static bool init[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return n;
+  if (!init[dev]) {
+    init[dev] = true;
+    // default: as much as the device allows; RNB_B200_L2_PERSIST_MB=0 turns the feature off
+    const char* e = getenv("RNB_B200_L2_PERSIST_MB");
+    const double mb = e ? atof(e) : 1e6;
+    if (mb > 0) {
+      int max_bytes = 0;
+      cudaDeviceGetAttribute(&max_bytes, cudaDevAttrMaxPersistingL2CacheSize, dev);
+      size_t want = (size_t)(mb * 1e6);
+      if (want > (size_t)max_bytes) want = (size_t)max_bytes;
+      if (want > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess)
+        carve[dev] = want;
+      (void)cudaGetLastError();
+    }
+  }
+  if (!carve[dev] || !ptr || !bytes) return n;
+  int max_window = 0;
+  cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+  size_t win = bytes;
+  if (max_window > 0 && win > (size_t)max_window) win = (size_t)max_window;
+  attr[n].id = cudaLaunchAttributeAccessPolicyWindow;
+  attr[n].val.accessPolicyWindow.base_ptr = const_cast<void*>(ptr);
+  attr[n].val.accessPolicyWindow.num_bytes = win;
+  static const double frac = [] {
+    const char* e = getenv("RNB_B200_L2_PERSIST_FRAC");
+    return e ? atof(e) : 0.9;
+  }();
+  const double ratio = (double)carve[dev] * frac / (double)win;
+  attr[n].val.accessPolicyWindow.hitRatio = ratio > 1.0 ? 1.0f : (float)ratio;
+  attr[n].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+  attr[n].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  return n + 1;
+}
 
 cudaError_t launch_conv_tc(const ConvTcParams& p, int num_sms, cudaStream_t stream) {
   const int smem = conv_tc_smem_bytes(p.bk, p.block_n, p.num_stages);

@@ -6,6 +6,7 @@
 
 #include <utility>
 
+#include "conv_tc.cuh"
 #include "ptx.cuh"
 
 namespace rnb {
@@ -15,6 +16,8 @@ namespace {
 // previous kernel in the stream drains (its prologue overlaps that tail; measured 0.9 us instead
 // of 4.1 us between kernels on a B200) and must execute griddepcontrol.wait before it touches
 // anything the previous kernel reads or writes.
+const void* g_pdl_window_ptr = nullptr;  // output of the next launch_pdl (L2 persistence), if any
+size_t g_pdl_window_bytes = 0;
 template <typename... KArgs, typename... Args>
 cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
                        Args&&... args) {
@@ -23,11 +26,13 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
   cfg.blockDim = block;
   cfg.dynamicSmemBytes = smem;
   cfg.stream = s;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = add_l2_output_window(attr, 1, g_pdl_window_ptr, g_pdl_window_bytes);
+  g_pdl_window_ptr = nullptr;
+  g_pdl_window_bytes = 0;
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 }  // namespace
@@ -483,6 +488,8 @@ cudaError_t launch_pre_u8_to_stem(const uint8_t* in, int batch, const float* sca
                                   const float* bias3, __nv_bfloat16* out, cudaStream_t s) {
   const int rows = batch * kClipT * kClipH;
   if (rows == 0) return cudaSuccess;
+  g_pdl_window_ptr = out;
+  g_pdl_window_bytes = (size_t)rows * (kClipW / 2) * kStemUnfold * 2;
   return launch_pdl(to_stem_kernel<uint8_t>, dim3((rows + kStemRows - 1) / kStemRows), dim3(256), 0,
                     s, in, rows, make_affine(scale3, bias3), reinterpret_cast<uint4*>(out), false);
 }
