@@ -410,10 +410,20 @@ int add_l2_output_window(cudaLaunchAttribute* attr, int n, const void* ptr, size
     const char* e = getenv("RNB_B200_L2_PERSIST_FRAC");
     return e ? atof(e) : 0.9;
   }();
+  static const double max_over = [] {  // skip tensors larger than this multiple of the carve-out
+    const char* e = getenv("RNB_B200_L2_PERSIST_MAX_OVER");
+    return e ? atof(e) : 1e9;
+  }();
+  static const int miss_normal = [] {
+    const char* e = getenv("RNB_B200_L2_PERSIST_MISS_NORMAL");
+    return e ? atoi(e) : 0;
+  }();
+  if ((double)bytes > max_over * (double)carve[dev]) return n;
   const double ratio = (double)carve[dev] * frac / (double)win;
   attr[n].val.accessPolicyWindow.hitRatio = ratio > 1.0 ? 1.0f : (float)ratio;
   attr[n].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-  attr[n].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  attr[n].val.accessPolicyWindow.missProp =
+      miss_normal ? cudaAccessPropertyNormal : cudaAccessPropertyStreaming;
   return n + 1;
 }
 

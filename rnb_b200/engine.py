@@ -275,9 +275,12 @@ class HostPipeline:
     """Feeds an engine from pinned host memory, end to end: host uint8 frames in, host logits out.
 
     The host->device copy of batch i+1 runs on a copy stream while batch i is in the network
-    (double-buffered device inputs, CUDA events in both directions); the logits go back to pinned
-    host memory on the compute stream.  This is the serving loop a caller without device-resident
-    data uses -- RnB's loader hands device tensors to the runner, so there the copy does not exist.
+    (double-buffered device inputs, CUDA events in both directions); the logits of batch i land in
+    a per-slot device buffer and go back to pinned host memory on a third stream, so the compute
+    stream runs kernel to kernel (a copy between two forwards would break the programmatic
+    dependent launch of the next staging kernel).  This is the serving loop a caller without
+    device-resident data uses -- RnB's loader hands device tensors to the runner, so there the
+    copy does not exist.
     """
 
     def __init__(self, engine, batch, depth=2):
@@ -285,8 +288,12 @@ class HostPipeline:
         self.depth = depth
         dev = engine.device
         self.copy_stream = torch.cuda.Stream(device=dev)
+        self.out_stream = torch.cuda.Stream(device=dev)
         self.dev_in = [torch.empty((batch, 8, 3, 112, 112), dtype=torch.uint8, device=dev)
                        for _ in range(depth)]
+        self.dev_out = [torch.empty((batch,) + engine.out_shape, dtype=torch.float32, device=dev)
+                        for _ in range(depth)]
+        self.fwd_done = [torch.cuda.Event() for _ in range(depth)]
         self.host_out = [torch.empty((batch,) + engine.out_shape, dtype=torch.float32).pin_memory()
                          for _ in range(depth)]
         self.in_ready = [torch.cuda.Event() for _ in range(depth)]
@@ -310,10 +317,17 @@ class HostPipeline:
             self.dev_in[slot][:n].copy_(host_frames, non_blocking=True)
             self.in_ready[slot].record(self.copy_stream)
         compute.wait_event(self.in_ready[slot])
-        logits = self.engine(self.dev_in[slot][:n])
+        # (slot reuse: result(slot) of the batch that used it has been waited for by the caller, or
+        # at least `depth` submits ago its read-back was queued before this forward's on out_stream)
+        if self.count >= self.depth:
+            compute.wait_event(self.out_ready[slot])
+        logits = self.engine(self.dev_in[slot][:n], out=self.dev_out[slot][:n])
         self.in_free[slot].record(compute)
-        self.host_out[slot][:n].copy_(logits, non_blocking=True)
-        self.out_ready[slot].record(compute)
+        self.fwd_done[slot].record(compute)
+        with torch.cuda.stream(self.out_stream):
+            self.out_stream.wait_event(self.fwd_done[slot])
+            self.host_out[slot][:n].copy_(logits, non_blocking=True)
+            self.out_ready[slot].record(self.out_stream)
         self.count += 1
         return slot
 
