@@ -377,53 +377,60 @@ cudaError_t launch_variant(const ConvTcParams& p, int num_sms, int smem, cudaStr
 }
 }  // namespace
 
-int add_l2_output_window(cudaLaunchAttribute* attr, int n, const void* ptr, size_t bytes) {
-  // carve-out size per device, set once (0 = feature off)
-  static size_t carve[64] = {};
-  static bool init[64] = {};
+namespace {
+struct L2PersistState {
+  bool init = false;
+  size_t max_carve = 0;  // what the device (and RNB_B200_L2_PERSIST_MB) allow
+  size_t carve = 0;      // current cudaLimitPersistingL2CacheSize set by this library (0 = off)
+  int max_window = 0;
+};
+L2PersistState g_l2[64];
+
+L2PersistState* l2_state() {
   int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return n;
-  if (!init[dev]) {
-    init[dev] = true;
-    // default: as much as the device allows; RNB_B200_L2_PERSIST_MB=0 turns the feature off
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  L2PersistState& st = g_l2[dev];
+  if (!st.init) {
+    st.init = true;
+    // default: as much as the device allows; RNB_B200_L2_PERSIST_MB caps it, 0 = feature off
     const char* e = getenv("RNB_B200_L2_PERSIST_MB");
     const double mb = e ? atof(e) : 1e6;
-    if (mb > 0) {
-      int max_bytes = 0;
-      cudaDeviceGetAttribute(&max_bytes, cudaDevAttrMaxPersistingL2CacheSize, dev);
-      size_t want = (size_t)(mb * 1e6);
-      if (want > (size_t)max_bytes) want = (size_t)max_bytes;
-      if (want > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess)
-        carve[dev] = want;
-      (void)cudaGetLastError();
-    }
+    int max_bytes = 0;
+    cudaDeviceGetAttribute(&max_bytes, cudaDevAttrMaxPersistingL2CacheSize, dev);
+    cudaDeviceGetAttribute(&st.max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+    size_t want = mb > 0 ? (size_t)(mb * 1e6) : 0;
+    if (want > (size_t)max_bytes) want = (size_t)max_bytes;
+    st.max_carve = want;
+    (void)cudaGetLastError();
   }
-  if (!carve[dev] || !ptr || !bytes) return n;
-  int max_window = 0;
-  cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+  return &st;
+}
+}  // namespace
+
+void l2_persist_configure(size_t largest_tensor_bytes) {
+  L2PersistState* st = l2_state();
+  if (!st || !st->max_carve) return;
+  // The carve-out is taken away from ordinary L2 capacity.  It pays while the largest tensor of a
+  // forward mostly fits (R18: +1.3 % at batch 16) and costs once the tensors outgrow it (-7 % at
+  // batch 32, -19 % at batch 64 with the carve-out left on): measured crossover ~1.5x.
+  const size_t want = (double)largest_tensor_bytes <= 1.5 * (double)st->max_carve ? st->max_carve : 0;
+  if (want == st->carve) return;
+  if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) st->carve = want;
+  (void)cudaGetLastError();
+}
+
+int add_l2_output_window(cudaLaunchAttribute* attr, int n, const void* ptr, size_t bytes) {
+  L2PersistState* st = l2_state();
+  if (!st || !st->carve || !ptr || !bytes) return n;
   size_t win = bytes;
-  if (max_window > 0 && win > (size_t)max_window) win = (size_t)max_window;
+  if (st->max_window > 0 && win > (size_t)st->max_window) win = (size_t)st->max_window;
   attr[n].id = cudaLaunchAttributeAccessPolicyWindow;
   attr[n].val.accessPolicyWindow.base_ptr = const_cast<void*>(ptr);
   attr[n].val.accessPolicyWindow.num_bytes = win;
-  static const double frac = [] {
-    const char* e = getenv("RNB_B200_L2_PERSIST_FRAC");
-    return e ? atof(e) : 0.9;
-  }();
-  static const double max_over = [] {  // skip tensors larger than this multiple of the carve-out
-    const char* e = getenv("RNB_B200_L2_PERSIST_MAX_OVER");
-    return e ? atof(e) : 1e9;
-  }();
-  static const int miss_normal = [] {
-    const char* e = getenv("RNB_B200_L2_PERSIST_MISS_NORMAL");
-    return e ? atoi(e) : 0;
-  }();
-  if ((double)bytes > max_over * (double)carve[dev]) return n;
-  const double ratio = (double)carve[dev] * frac / (double)win;
+  const double ratio = (double)st->carve * 0.9 / (double)win;
   attr[n].val.accessPolicyWindow.hitRatio = ratio > 1.0 ? 1.0f : (float)ratio;
   attr[n].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-  attr[n].val.accessPolicyWindow.missProp =
-      miss_normal ? cudaAccessPropertyNormal : cudaAccessPropertyStreaming;
+  attr[n].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
   return n + 1;
 }
 

@@ -75,8 +75,11 @@ cudaError_t launch_conv_tc(const ConvTcParams& p, int num_sms, cudaStream_t stre
 // "persisting" through a per-launch access-policy window, so that the next kernel -- its only
 // consumer -- finds as much of it as fits the carve-out still in L2 instead of re-reading it from
 // HBM (measured +1.5-3.5 % on the R18 batch-16 step).  The carve-out is the device maximum
-// (cudaLimitPersistingL2CacheSize, set once per device; RNB_B200_L2_PERSIST_MB caps it, 0 = off).
-// Appends the attribute to attr[n] and returns the new count.
+// (cudaLimitPersistingL2CacheSize; RNB_B200_L2_PERSIST_MB caps it, 0 = off) while the largest
+// tensor of the forward mostly fits it, and zero otherwise: l2_persist_configure(), called before
+// the launches of a forward, switches it when the batch size changes regime.
+// add_l2_output_window appends the attribute to attr[n] and returns the new count.
+void l2_persist_configure(size_t largest_tensor_bytes);
 int add_l2_output_window(cudaLaunchAttribute* attr, int n, const void* ptr, size_t bytes);
 
 // Split-K variant: the fp32 staging area of the reduction (block_n x 128) aliases the operand ring.

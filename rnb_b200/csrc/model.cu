@@ -811,6 +811,13 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
     plan = ensure_plan(batch, stream, err);
     last_batch_ = batch;
     if (!plan) return RNB_ECUDA;
+    // L2 persistence carve-out on or off for this batch size (conv_tc.cuh)
+    size_t largest = 0;
+    for (const ConvOp& op : ops_) {
+      const size_t b = (size_t)op.g.out_elems(batch) * 2;
+      if (b > largest) largest = b;
+    }
+    l2_persist_configure(largest);
   }
   cudaError_t e = cudaSuccess;
   mark();
