@@ -22,6 +22,24 @@
 
 namespace rnb {
 
+#ifdef RNB_PATCH_COUNTERS
+// development aid (make test_conv_cnt): cycles CTA 0's producer and MMA warps spend waiting
+__device__ unsigned long long g_pair_cnt[8];
+void pair_counters_read_reset(unsigned long long out[8]) {
+  cudaMemcpyFromSymbol(out, g_pair_cnt, sizeof(g_pair_cnt));
+  unsigned long long z[8] = {};
+  cudaMemcpyToSymbol(g_pair_cnt, z, sizeof(z));
+}
+#define PCNT(i, stmt)                                              \
+  {                                                                \
+    const long long pc_t0 = clock64();                             \
+    stmt;                                                          \
+    pc_acc[i] += (unsigned long long)(clock64() - pc_t0);          \
+  }
+#else
+#define PCNT(i, stmt) stmt
+#endif
+
 namespace {
 
 struct PairTile {
@@ -112,6 +130,9 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (warp-wide)
     uint32_t stage = 0, phase = 0;
+#ifdef RNB_PATCH_COUNTERS
+    unsigned long long pc_acc[8] = {};
+#endif
     for (int item = first_item; item < total_items; item += item_step) {
       const PairTile tc = pair_decode(p, item, rank);
       // my rows of the channel tile: the MMA takes columns [0, N/2) from the leader's shared
@@ -122,7 +143,7 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
         const int cw = tc.w0 + p.tap_dw[tap], ch = tc.h0 + p.tap_dh[tap], ct = tc.t0 + p.tap_dt[tap];
         const int coff = p.tap_coff[tap], koff = p.tap_koff[tap];
         for (int kb = 0; kb < p.tap_nkb[tap]; ++kb) {
-          ptx::mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+          PCNT(0, ptx::mbar_wait(empty_bar + 8 * stage, phase ^ 1));
           const uint32_t fb = full_ld + 8 * stage;
           const uint32_t sa = smem_base + stage * stage_bytes;
           // the leader announces the bytes of both CTAs
@@ -136,24 +157,33 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
         }
       }
     }
+#ifdef RNB_PATCH_COUNTERS
+    if (blockIdx.x == 0 && lane == 0) g_pair_cnt[0] += pc_acc[0];
+#endif
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (leader only)
     if (rank == 0) {
       const uint32_t swz = p.bk * 2;
       uint32_t stage = 0, phase = 0;
       int local = 0;
+#ifdef RNB_PATCH_COUNTERS
+      unsigned long long pc_acc[8] = {};
+      const long long pc_loop0 = clock64();
+      unsigned long long pc_g0;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(pc_g0));
+#endif
       for (int item = first_item; item < total_items; item += item_step, ++local) {
         const int ncols = min(p.block_n, p.cout_pad - (item % p.n_tiles) * p.block_n);
         const uint32_t idesc = ptx::make_idesc_bf16_m256((uint32_t)ncols);
         const uint32_t acc = local & 1;
         const uint32_t acc_phase = (local >> 1) & 1;
         const uint32_t tmem_d = tmem_base + acc * kMaxBlockN;
-        ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1);
+        PCNT(1, ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1));
         ptx::tc_fence_after();
         uint32_t accumulate = 0;
         for (int tap = 0; tap < p.num_taps; ++tap) {
           for (int kb = 0; kb < p.tap_nkb[tap]; ++kb) {
-            ptx::mbar_wait(full_bar + 8 * stage, phase);
+            PCNT(2, ptx::mbar_wait(full_bar + 8 * stage, phase));
             ptx::tc_fence_after();
             const uint32_t sa = smem_base + stage * stage_bytes;
             const uint64_t adesc = ptx::make_kmajor_desc(sa, swz);
@@ -173,6 +203,17 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
         }
         ptx::umma_commit_pair_elect(tmem_full_bar + 8 * acc, 3);  // both epilogues may start
       }
+#ifdef RNB_PATCH_COUNTERS
+      if (blockIdx.x == 0 && lane == 0) {
+        unsigned long long pc_g1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(pc_g1));
+        g_pair_cnt[1] += pc_acc[1];
+        g_pair_cnt[2] += pc_acc[2];
+        g_pair_cnt[3] += (unsigned long long)local;
+        g_pair_cnt[6] += (unsigned long long)(clock64() - pc_loop0);
+        g_pair_cnt[7] += pc_g1 - pc_g0;
+      }
+#endif
     }
   } else {
     // ------------------------------------------------------------------ epilogue (256 threads)

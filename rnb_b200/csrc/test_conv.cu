@@ -17,6 +17,7 @@ using namespace rnb;
 namespace rnb {
 void patch_counters_read_reset(unsigned long long out[8]);
 void patch_epi_read_reset(unsigned long long out[8]);
+void pair_counters_read_reset(unsigned long long out[8]);
 void patch_cta_times(unsigned long long out[4][3][256]);
 void patch_cta_smids(unsigned int out[4][256]);
 }
@@ -394,6 +395,23 @@ static bool run_case(const Case& c, int perf_iters) {
       CK(cudaEventElapsedTime(&ms, e0, e1));
       const double us = ms * 1e3 / perf_iters;
       printf("    CTA-pair N<=%d perf: %.1f us  %.1f TFLOP/s\n", cap, us, g.flops(B) / us * 1e-6);
+#ifdef RNB_PATCH_COUNTERS
+      {
+        unsigned long long pc[8];
+        pair_counters_read_reset(pc);
+        CK(launch_conv_pair(sp, num_sms, 0));
+        CK(cudaDeviceSynchronize());
+        pair_counters_read_reset(pc);
+        const double it = pc[3] > 0 ? (double)pc[3] : 1.0;
+        const double kbs = (double)sp.num_taps * sp.kb_per_tap;
+        printf("      pair CTA 0: %.0f items; per item: producer wait empty %.0f | mma wait tmem_empty "
+               "%.0f, wait full %.0f (%.0f per K block) | loop %.0f cycles = %.2f us (%.0f MHz); "
+               "MMA floor %.0f cycles\n",
+               it, pc[0] / it, pc[1] / it, pc[2] / it, pc[2] / it / kbs, pc[6] / it,
+               pc[7] * 1e-3 / it, (double)pc[6] / (pc[7] * 1e-3),
+               kbs * 4 * (sp.block_n >= 128 ? sp.block_n / 2.0 : 48.7));
+      }
+#endif
     }
   }
   cudaFree(dx); cudaFree(dw); cudaFree(dscale); cudaFree(dshift); cudaFree(dy); cudaFree(dxb);
@@ -532,6 +550,7 @@ int main(int argc, char** argv) {
       {"conv5 temporal 1152->512 +res", geom(1, 7, 7, 1152, 512, 3, 1, 1, 1, 1, 1, 1, 0, 0), 3, true, true},
       {"stem temporal 83->64", geom(8, 56, 56, 83, 64, 3, 1, 1, 1, 1, 1, 1, 0, 0), 1, false, false},
       {"conv2 temporal 144->64", geom(8, 56, 56, 144, 64, 3, 1, 1, 1, 1, 1, 1, 0, 0), 1, true, false},
+      {"conv3 temporal 288->128", geom(4, 28, 28, 288, 128, 3, 1, 1, 1, 1, 1, 1, 0, 0), 2, true, false},
   };
   int failed = 0;
   for (const Case& c : cases) failed += run_case(c, 0) ? 0 : 1;
