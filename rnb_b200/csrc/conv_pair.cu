@@ -80,8 +80,10 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
   const int lane = threadIdx.x & 31;
   const uint32_t rank = blockIdx.x & 1u;  // (2,1,1) cluster over a 1-D grid; provably uniform
 
-  const uint32_t a_bytes = kTileM * p.bk * 2;
-  const uint32_t b_bytes = (p.block_n / 2) * p.bk * 2;  // my half of the weight tile
+  // temporal-patch mode: tp_rows activation rows and three weight tiles (one per tap) per stage
+  const uint32_t a_bytes = p.tpatch ? (uint32_t)p.tp_rows * 128u : kTileM * p.bk * 2;
+  const uint32_t b_tile = (p.block_n / 2) * p.bk * 2;  // my half of one weight tile
+  const uint32_t b_bytes = p.tpatch ? 3u * b_tile : b_tile;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t bars = smem_base + p.num_stages * stage_bytes;
   const uint32_t full_bar = bars;
@@ -138,6 +140,25 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
       // my rows of the channel tile: the MMA takes columns [0, N/2) from the leader's shared
       // memory and [N/2, N) from the peer's
       const int brow = tc.n0 + rank * (tc.ncols / 2);
+      if (p.tpatch) {
+        for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+          PCNT(0, ptx::mbar_wait(empty_bar + 8 * stage, phase ^ 1));
+          const uint32_t fb = full_ld + 8 * stage;
+          const uint32_t sa = smem_base + stage * stage_bytes;
+          if (rank == 0) ptx::mbar_expect_tx_elect(full_bar + 8 * stage, 2 * stage_bytes);
+          // frames t0 - 1 .. t0 + tile frames: the halo lies outside the tensor at the clip's ends
+          // and is zero-filled, which is the convolution's temporal padding
+          ptx::tma_load_5d_pair_elect(sa, &p.a_map[0], fb, kb * p.bk, tc.w0, 0, tc.t0 - 1, tc.b0);
+          for (int tap = 0; tap < 3; ++tap)
+            ptx::tma_load_2d_pair_elect(sa + a_bytes + tap * b_tile, &p.b_map, fb,
+                                        tap * p.cin_pad + kb * p.bk, brow);
+          if (++stage == (uint32_t)p.num_stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        continue;
+      }
       for (int tap = 0; tap < p.num_taps; ++tap) {
         const void* amap = &p.a_map[p.tap_map[tap]];
         const int cw = tc.w0 + p.tap_dw[tap], ch = tc.h0 + p.tap_dh[tap], ct = tc.t0 + p.tap_dt[tap];
@@ -181,7 +202,31 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
         PCNT(1, ptx::mbar_wait(tmem_empty_bar + 8 * acc, acc_phase ^ 1));
         ptx::tc_fence_after();
         uint32_t accumulate = 0;
-        for (int tap = 0; tap < p.num_taps; ++tap) {
+        if (p.tpatch) {
+          for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+            PCNT(2, ptx::mbar_wait(full_bar + 8 * stage, phase));
+            ptx::tc_fence_after();
+            const uint32_t sa = smem_base + stage * stage_bytes;
+            const int ksteps = min(p.bk, p.cin_pad - kb * p.bk) >> 4;
+            for (int tap = 0; tap < 3; ++tap) {
+              // tap dt = the same rows, tp_shift rows (one frame of the tile) further on
+              const uint64_t adesc =
+                  ptx::make_kmajor_desc(sa + (uint32_t)(tap * p.tp_shift) * 128u, swz);
+              const uint64_t bdesc = ptx::make_kmajor_desc(sa + a_bytes + tap * b_tile, swz);
+              ptx::umma_bf16_pair_elect(tmem_d, adesc, bdesc, idesc, accumulate);
+              if (ksteps > 1) ptx::umma_bf16_pair_elect(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
+              if (ksteps > 2) ptx::umma_bf16_pair_elect(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
+              if (ksteps > 3) ptx::umma_bf16_pair_elect(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
+              accumulate = 1;
+            }
+            ptx::umma_commit_pair_elect(empty_bar + 8 * stage, 3);
+            if (++stage == (uint32_t)p.num_stages) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+        }
+        for (int tap = 0; tap < (p.tpatch ? 0 : p.num_taps); ++tap) {
           for (int kb = 0; kb < p.tap_nkb[tap]; ++kb) {
             PCNT(2, ptx::mbar_wait(full_bar + 8 * stage, phase));
             ptx::tc_fence_after();
@@ -344,7 +389,9 @@ cudaError_t launch_pair_variant(const ConvTcParams& p, int num_sms, int smem, cu
 
 cudaError_t launch_conv_pair(const ConvTcParams& p, int num_sms, cudaStream_t stream) {
   if (!p.pair || p.cm != 1 || p.cn != 1 || p.ks > 1 || (p.block_n & 15)) return cudaErrorInvalidValue;
-  const int smem = conv_pair_smem_bytes(p.bk, p.block_n, p.num_stages);
+  const int smem =
+      p.tpatch ? 1024 + p.num_stages * conv_tpatch_stage_bytes(p.tp_rows, p.block_n) + 256 + kMaxBlockN * 4
+               : conv_pair_smem_bytes(p.bk, p.block_n, p.num_stages);
   if (smem > kSmemLimit) return cudaErrorInvalidValue;
   const bool res = p.residual != nullptr, relu = p.relu != 0;
   if (res && relu) return launch_pair_variant<true, true>(p, num_sms, smem, stream);

@@ -47,6 +47,11 @@ struct ConvTcParams {
   // CTA-pair variant (conv_pair.cu): two CTAs on neighbouring position tiles share one channel tile,
   // each loading half of it, one tcgen05.mma.cta_group::2 (M = 256).  0: not paired.
   int pair;
+  // Temporal-patch mode of the CTA-pair kernel (3x1x1, stride 1): a pipeline stage holds, for one
+  // 64-channel block, the tile's frames plus one halo frame on either side (tp_rows rows, loaded
+  // ONCE) and the weight tiles of all three taps; tap dt reads the rows from dt * tp_shift on.
+  // The spatial extent is flattened (Wo = H*W, Ho = 1).  0: off.
+  int tpatch, tp_rows, tp_shift;
   int m_tiles;
   int a_slice_dim, a_slice_step;
   int8_t tap_map[kMaxTaps];
@@ -94,6 +99,9 @@ cudaError_t launch_conv_splitk(const ConvTcParams& p, int num_sms, cudaStream_t 
 inline int conv_pair_stage_bytes(int bk, int block_n) { return (kTileM + block_n / 2) * bk * 2; }
 inline int conv_pair_smem_bytes(int bk, int block_n, int stages) {
   return 1024 + stages * conv_pair_stage_bytes(bk, block_n) + 256 + kMaxBlockN * 4;
+}
+inline int conv_tpatch_stage_bytes(int tp_rows, int block_n) {
+  return tp_rows * 128 + 3 * (block_n / 2) * 128;
 }
 cudaError_t launch_conv_pair(const ConvTcParams& p, int num_sms, cudaStream_t stream);
 

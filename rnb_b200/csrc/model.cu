@@ -493,6 +493,9 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
     const bool ok = like->patch
                         ? build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
                                                   &out->pp, &perr)
+                    : like->tc.tpatch
+                        ? build_conv_tpatch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
+                                                   like->tc.block_n, &out->tc, &perr)
                         : build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
                                                num_sms_, &out->tc, &perr, like->tc.cm, like->tc.cn,
                                                like->tc.ks, like->tc.block_n, like->tc.pair, xe);
@@ -624,6 +627,36 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
       }
     }
   }
+  // temporal-patch mode of the CTA-pair kernel: wide 3x1x1 stride-1 layers (conv3 temporal).
+  // Opt-in (RNB_B200_TPATCH=1): 15.3 -> 12.9 us on conv3's temporal layers in isolation but no
+  // measurable change of the step, and its K order (block-outer, tap-inner) differs from the other
+  // kernels', which costs the bit-identical rows across batch sizes.
+  static const bool allow_tpatch = [] {
+    const char* e = getenv("RNB_B200_TPATCH");
+    return e && e[0] == '1';
+  }();
+  if (allow_tpatch && allow_pair && !failed && ok && conv_tpatch_applicable(op.g)) {
+    int seen_n = 0;
+    for (int cap : {256, 128}) {
+      ConvTcParams trial;
+      std::string serr;
+      if (!build_conv_tpatch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, cap, &trial,
+                                    &serr))
+        continue;
+      if (trial.block_n == seen_n) continue;
+      seen_n = trial.block_n;
+      float ms = 0.f;
+      if (!time_it([&] { return launch_conv_pair(trial, num_sms_, stream); }, &ms)) {
+        failed = true;
+        break;
+      }
+      if (ms < best_ms * 0.97f) {
+        best_ms = ms;
+        out->patch = false;
+        out->tc = trial;
+      }
+    }
+  }
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   if (failed || !ok) return fail(perr.empty() ? "no launch candidate" : perr);
@@ -720,9 +753,10 @@ bool R2P1DModel::load_cached_plan(const char* path, int batch, cudaStream_t stre
     if (sscanf(line, "plan %llx %d", &key, &n) != 2 || key != want || n != (int)ops_.size()) continue;
     found = true;
     for (int i = 0; i < n && found; ++i) {
-      int op = -1, patch = 0, cm = 1, cn = 1, ks = 0, bn = 0, pair = 0;
+      int op = -1, patch = 0, cm = 1, cn = 1, ks = 0, bn = 0, pair = 0, tpatch = 0;
       if (!fgets(line, sizeof line, f) ||
-          sscanf(line, "%d %d %d %d %d %d %d", &op, &patch, &cm, &cn, &ks, &bn, &pair) != 7 ||
+          sscanf(line, "%d %d %d %d %d %d %d %d", &op, &patch, &cm, &cn, &ks, &bn, &pair,
+                 &tpatch) < 7 ||
           op != i) {
         found = false;
         break;
@@ -734,6 +768,7 @@ bool R2P1DModel::load_cached_plan(const char* path, int batch, cudaStream_t stre
       like.tc.ks = ks;
       like.tc.block_n = bn;
       like.tc.pair = pair;
+      like.tc.tpatch = tpatch;
       std::string e;
       if (!plan_conv(i, 0, batch, false, stream, &like, &l, &e)) found = false;
       plan->push_back(l);
@@ -751,8 +786,8 @@ void R2P1DModel::save_cached_plan(const char* path, int batch, const std::vector
   if (!f) return;
   fprintf(f, "plan %llx %d\n", (unsigned long long)plan_key(batch), (int)plan.size());
   for (const Launch& l : plan)
-    fprintf(f, "%d %d %d %d %d %d %d\n", l.op, l.patch ? 1 : 0, l.tc.cm, l.tc.cn, l.tc.ks,
-            l.tc.block_n, l.tc.pair);
+    fprintf(f, "%d %d %d %d %d %d %d %d\n", l.op, l.patch ? 1 : 0, l.tc.cm, l.tc.cn, l.tc.ks,
+            l.tc.block_n, l.tc.pair, l.tc.tpatch);
   fclose(f);
 }
 

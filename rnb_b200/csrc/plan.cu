@@ -437,6 +437,101 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
 }
 
 namespace {
+int ilog2_tp(int v) {
+  int l = 0;
+  while ((1 << l) < v) ++l;
+  return l;
+}
+}  // namespace
+
+bool conv_tpatch_applicable(const ConvGeom& g) {
+  return !g.stem_unfolded && g.kt == 3 && g.kh == 1 && g.kw == 1 && g.st == 1 && g.sh == 1 &&
+         g.sw == 1 && g.pt == 1 && g.ph == 0 && g.pw == 0 && g.To >= 2 && g.To == g.Ti &&
+         !g.extra_cin && !g.ncat;
+}
+
+bool build_conv_tpatch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
+                              const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
+                              const __nv_bfloat16* residual, bool relu, int n_cap, ConvTcParams* out,
+                              std::string* err) {
+  if (!conv_tpatch_applicable(g)) {
+    if (err) *err = "conv_tpatch: geometry not supported";
+    return false;
+  }
+  ConvTcParams& p = *out;
+  memset(&p, 0, sizeof p);
+  const int cp = g.cin_pad(), np = g.cout_pad();
+  const int hw = g.Ho * g.Wo;
+  // tile: tt frames of pt consecutive positions of the flattened H x W plane (a 3x1x1 filter does
+  // not care about the spatial structure, and 28 x 28 or 14 x 14 planes tile badly as boxes)
+  const int tt = g.To >= 8 ? 8 : (g.To >= 4 ? 4 : 2);
+  const int pt = 128 / tt;
+  p.shift = shift;
+  p.residual = residual;
+  p.y = y;
+  p.relu = relu ? 1 : 0;
+  p.cin_pad = cp;
+  p.bk = 64;
+  p.kb_per_tap = ceil_div(cp, 64);
+  p.num_taps = 3;
+  p.Wo = hw;
+  p.Ho = 1;
+  p.To = g.To;
+  p.B = B;
+  p.cout_pad = np;
+  p.lbw = ilog2_tp(pt);
+  p.lbh = 0;
+  p.lbt = ilog2_tp(tt);
+  p.tiles_w = ceil_div(hw, pt);
+  p.tiles_h = 1;
+  p.tiles_t = ceil_div(g.To, tt);
+  p.tiles_b = B;
+  p.m_tiles = p.tiles_w * p.tiles_t * p.tiles_b;
+  if (p.m_tiles < 2) {
+    if (err) *err = "conv_tpatch: CTA pairs need two position tiles";
+    return false;
+  }
+  const int cap = n_cap >= 16 && n_cap < kMaxBlockN ? n_cap : kMaxBlockN;
+  const int nt = ceil_div(np, cap);
+  p.block_n = round_up(ceil_div(np, nt), 16);
+  p.n_tiles = ceil_div(np, p.block_n);
+  p.cm = p.cn = 1;
+  p.pair = 1;
+  p.tpatch = 1;
+  p.tp_rows = (tt + 2) * pt;
+  p.tp_shift = pt;
+  const int stage = conv_tpatch_stage_bytes(p.tp_rows, p.block_n);
+  int stages = (kSmemLimit - 1024 - 256 - kMaxBlockN * 4) / stage;
+  if (stages > 10) stages = 10;
+  if (stages < 2) {
+    if (err) *err = "conv_tpatch: pipeline does not fit in shared memory";
+    return false;
+  }
+  p.num_stages = stages;
+  for (int tap = 0; tap < 3; ++tap) {
+    p.tap_koff[tap] = tap * cp;
+    p.tap_cin[tap] = (int16_t)cp;
+    p.tap_nkb[tap] = (int8_t)p.kb_per_tap;
+  }
+  {
+    const uint64_t pc = (uint64_t)(g.in_pitch ? g.in_pitch : cp);
+    const uint64_t dims[5] = {pc, (uint64_t)hw, 1, (uint64_t)g.Ti, (uint64_t)B};
+    const uint64_t strides[4] = {pc * 2, (uint64_t)hw * pc * 2, (uint64_t)hw * pc * 2,
+                                 (uint64_t)g.Ti * hw * pc * 2};
+    const uint32_t box[5] = {64u, (uint32_t)pt, 1u, (uint32_t)(tt + 2), 1u};
+    if (!encode_bf16(&p.a_map[0], x, 5, dims, strides, box, 128, err)) return false;
+    for (int v = 1; v < 4; ++v) p.a_map[v] = p.a_map[0];
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)np};
+    const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
+    const uint32_t box[2] = {64u, (uint32_t)(p.block_n / 2)};
+    if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, 128, err)) return false;
+  }
+  return true;
+}
+
+namespace {
 struct PatchShape {
   bool ok = false;
   bool spatial = false;

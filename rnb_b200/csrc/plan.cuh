@@ -80,6 +80,15 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
 // split_n caps its channel tile, default = the accumulator width; pair = 1 plans the CTA-pair
 // variant, conv_pair.cu, whose channel tile split_n caps as well)
 
+// Temporal-patch mode of the CTA-pair kernel (conv_pair.cu): 3x1x1 stride-1 convolutions whose
+// input is too wide for the patch kernel (conv3 / conv4 temporal).  Each 64-channel block of the
+// tile's frames + halo is loaded once and serves all three taps.  n_cap caps the channel tile.
+bool conv_tpatch_applicable(const ConvGeom& g);
+bool build_conv_tpatch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
+                              const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
+                              const __nv_bfloat16* residual, bool relu, int n_cap, ConvTcParams* out,
+                              std::string* err);
+
 // Patch kernel (conv_patch.cuh): stride-1 1x3x3 and 3x1x1 convolutions; weights resident in shared
 // memory when they fit next to two activation patches, streamed otherwise.  pair = 1 plans the
 // CTA-pair (cta_group::2) variant, in which each CTA holds half of every weight tile.

@@ -414,6 +414,56 @@ static bool run_case(const Case& c, int perf_iters) {
 #endif
     }
   }
+  // ---- the temporal-patch mode of the CTA-pair kernel
+  if (conv_tpatch_applicable(g)) {
+    for (int cap : {256, 128}) {
+      ConvTcParams sp;
+      std::string serr;
+      if (!build_conv_tpatch_params(g, B, dxb, dwp, dyb, dshift, drb, c.relu, cap, &sp, &serr)) {
+        printf("    temporal-patch plan (N<=%d): %s\n", cap, serr.c_str());
+        continue;
+      }
+      if (cap == 128 && sp.block_n > 128) continue;
+      CK(cudaMemset(dyb, 0xff, out_pos * np * 2));
+      CK(launch_conv_pair(sp, num_sms, 0));
+      CK(cudaDeviceSynchronize());
+      CK(cudaMemcpy(yb.data(), dyb, yb.size() * 2, cudaMemcpyDeviceToHost));
+      double serr_max = 0;
+      size_t sbad = 0, snan = 0;
+      for (size_t i = 0; i < out_pos; ++i)
+        for (int ch = 0; ch < np; ++ch) {
+          const float t = bf16_bits_to_f32(yb[i * np + ch]);
+          if (ch >= g.cout) {
+            if (t != 0.f) ++sbad;
+            continue;
+          }
+          const double e = fabs((double)t - yr[i * g.cout + ch]);
+          if (!(e == e)) ++snan;
+          if (!(e <= serr_max)) serr_max = e;
+        }
+      const bool ok = serr_max / (max_ref > 0 ? max_ref : 1) < 1e-2 && sbad == 0 && snan == 0;
+      printf("    temporal-patch pair (N=%dx%d, %d stages, %d rows/stage): max|err|=%.4f pad_bad=%zu "
+             "nan=%zu  %s\n",
+             sp.n_tiles, sp.block_n, sp.num_stages, sp.tp_rows, serr_max, sbad, snan,
+             ok ? "PASS" : "FAIL");
+      sk_pass = sk_pass && ok;
+      if (ok && perf_iters > 0) {
+        cudaEvent_t e0, e1;
+        CK(cudaEventCreate(&e0));
+        CK(cudaEventCreate(&e1));
+        for (int i = 0; i < 3; ++i) CK(launch_conv_pair(sp, num_sms, 0));
+        CK(cudaEventRecord(e0));
+        for (int i = 0; i < perf_iters; ++i) CK(launch_conv_pair(sp, num_sms, 0));
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        const double us = ms * 1e3 / perf_iters;
+        printf("    temporal-patch N<=%d perf: %.1f us  %.1f TFLOP/s\n", cap, us,
+               g.flops(B) / us * 1e-6);
+      }
+    }
+  }
   cudaFree(dx); cudaFree(dw); cudaFree(dscale); cudaFree(dshift); cudaFree(dy); cudaFree(dxb);
   cudaFree(dwp); cudaFree(dyb);
   if (dres) cudaFree(dres);
