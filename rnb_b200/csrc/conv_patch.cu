@@ -230,18 +230,6 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
     uint32_t rlocal = 0;
     for (int item = first_item; item < total_items; item += item_step) {
       const PatchItem tc = decode_patch_item(p, item, kNumCta, rank);
-      // L2 prefetch of the patch `p.prefetch` items ahead: its real load can only be issued when a
-      // patch buffer frees, about one tile before it is needed, which is less than the DRAM
-      // latency; with the prefetch that load hits L2
-      if (p.prefetch > 0) {
-        const int ahead = item + p.prefetch * item_step;
-        if (ahead < total_items) {
-          const PatchItem ta = decode_patch_item(p, ahead, kNumCta, rank);
-          for (int kb = 0; kb < p.nkb; ++kb)
-            ptx::tma_prefetch_5d_elect(&p.a_map, kb * 64, ta.w0 + p.aw, ta.h0 + p.ah, ta.t0 + p.at,
-                                       ta.b);
-        }
-      }
       {
         CNT_BEGIN();
         ptx::mbar_wait(p_empty + 8 * pb, ph ^ 1);
@@ -516,9 +504,6 @@ conv_patch_kernel(const __grid_constant__ ConvPatchParams p) {
 #ifdef RNB_PATCH_COUNTERS
     if (blockIdx.x == 0 && warp == 2 && lane == 0)
       for (int k = 0; k < 6; ++k) g_patch_epi[k] += epi_cnt[k];
-#ifdef RNB_EXIT_FENCE
-    __threadfence();  // experiment: is the exit->entry turnaround the drain of the output stores?
-#endif
 #endif
   }
 

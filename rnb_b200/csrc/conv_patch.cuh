@@ -50,7 +50,6 @@ struct ConvPatchParams {
   int n_tiles, block_n; // channel tiling: resident mode has one tile of n channels
   int b_stages;         // 0: weights resident; > 0: ring depth of the streamed weight tiles
   int p_bufs;           // patch ring depth (2..kPatchMaxBufs)
-  int prefetch;         // L2-prefetch the patch this many items ahead (0 = off)
 #ifdef RNB_PATCH_COUNTERS
   int dbg_launch;       // which of the 4 timestamp sets this launch writes
 #endif

@@ -141,20 +141,10 @@ __device__ __forceinline__ void epilogue_tile(uint32_t full_bar, uint32_t full_p
     EPI_MARK(3);
     uint32_t o[8];
     epi::finish16<kRes, kRelu>(va, sa, ra, o);
-#ifdef RNB_NO_STORES
-    if (valid && o[0] == 0x12345678u && o[1] == 0x9abcdef0u)  // experiment: (almost) never stores
-#else
-    if (valid)
-#endif
-      ptx::st_global_v8(out_row + c0 * 16, o);
+    if (valid) ptx::st_global_v8(out_row + c0 * 16, o);
     if (two) {
       epi::finish16<kRes, kRelu>(vb, sb, rb, o);
-#ifdef RNB_NO_STORES
-      if (valid && o[0] == 0x12345678u && o[1] == 0x9abcdef0u)
-#else
-      if (valid)
-#endif
-        ptx::st_global_v8(out_row + c1 * 16, o);
+      if (valid) ptx::st_global_v8(out_row + c1 * 16, o);
     }
     if (kRes) {
 #pragma unroll

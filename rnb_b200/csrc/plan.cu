@@ -681,14 +681,6 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   p.block_n = s.block_n;
   p.b_stages = s.b_stages;
   p.p_bufs = s.p_bufs;
-  {
-    // items ahead to prefetch into L2 (RNB_B200_PATCH_PREFETCH overrides; 0 disables)
-    static const int pf = [] {
-      const char* e = getenv("RNB_B200_PATCH_PREFETCH");
-      return e ? atoi(e) : 0;
-    }();
-    p.prefetch = s.n_tiles == 1 ? pf : 0;  // with channel tiles the same patch is re-read anyway
-  }
   p.pair = pair ? 1 : 0;
   p.tw = s.tw; p.th = s.th; p.tt = s.tt;
   p.lpw = s.lpw; p.lph = s.lph;

@@ -108,18 +108,6 @@ __device__ __forceinline__ void tma_load_5d(uint32_t dst, const void* tmap, uint
       "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
       : "memory");
 }
-// L2 prefetch of a tensor box (no shared memory, no barrier): hides DRAM latency for a box that
-// will be loaded for real a few tiles later
-__device__ __forceinline__ void tma_prefetch_5d_elect(const void* tmap, int c0, int c1, int c2, int c3,
-                                                      int c4) {
-  asm volatile(
-      "{\n\t.reg .pred q;\n\t"
-      "elect.sync _|q, 0xffffffff;\n\t"
-      "@q cp.async.bulk.prefetch.tensor.5d.L2.global.tile [%0, {%1, %2, %3, %4, %5}];\n\t}\n" ::"l"(
-          reinterpret_cast<uint64_t>(tmap)),
-      "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
-      : "memory");
-}
 __device__ __forceinline__ void tma_store_5d(const void* tmap, uint32_t src, int c0, int c1, int c2,
                                              int c3, int c4) {
   asm volatile(

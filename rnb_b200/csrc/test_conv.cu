@@ -200,7 +200,7 @@ static bool run_case(const Case& c, int perf_iters) {
              pp.b_stages ? "streamed" : "resident", pp.p_bufs, pp.b_stages, pp.tail_ch, pp.res_smem, perr, pbad,
              nanc,
              ok ? "PASS" : "FAIL");
-      if ((ok || getenv("RNB_FORCE_PERF")) && perf_iters > 0) {
+      if (ok && perf_iters > 0) {
         cudaEvent_t e0, e1;
         CK(cudaEventCreate(&e0));
         CK(cudaEventCreate(&e1));
@@ -606,7 +606,7 @@ int main(int argc, char** argv) {
   for (const Case& c : cases) failed += run_case(c, 0) ? 0 : 1;
   failed += run_stem(2) ? 0 : 1;
 
-  if (perf_batch > 0 && (failed == 0 || getenv("RNB_FORCE_PERF"))) {
+  if (perf_batch > 0 && failed == 0) {
     printf("---- perf at B=%d\n", perf_batch);
     for (Case c : cases) {
       if (c.g.Hi < 7 || c.g.Hi == 8) continue;
