@@ -565,6 +565,34 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
       ok = true;
     }
   }
+  // One-wave channel tiling for the tap kernel: when there are fewer position tiles than SMs, a
+  // channel tile chosen so that position tiles x channel tiles just fits the SM count avoids a
+  // mostly empty second wave (conv4 temporal: 49 x 3 tiles of 96/96/64 channels = 147 CTAs).
+  if (!failed && ok) {
+    ConvTcParams probe;
+    std::string serr;
+    if (build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &probe, &serr,
+                             1, 1, 0, 0, 0, xe) &&
+        probe.m_tiles < num_sms_) {
+      const int nt = num_sms_ / probe.m_tiles;
+      int bn = (op.g.cout_pad() + nt - 1) / nt;
+      bn = (bn + 15) / 16 * 16;
+      if (bn > kMaxBlockN) bn = kMaxBlockN;
+      ConvTcParams trial;
+      if (bn >= 32 && bn != probe.block_n &&
+          build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &trial,
+                               &serr, 1, 1, 0, bn, 0, xe)) {
+        float ms = 0.f;
+        if (!time_it([&] { return launch_conv_tc(trial, num_sms_, stream); }, &ms)) {
+          failed = true;
+        } else if (ms < best_ms * 0.97f) {
+          best_ms = ms;
+          out->patch = false;
+          out->tc = trial;
+        }
+      }
+    }
+  }
   // split-K (conv_splitk.cu) where the tap kernel's grid leaves SMs idle or re-streams the
   // operands of narrow channel tiles: clusters of 2-4 CTAs per output tile, wide or medium tiles.
   // RNB_B200_SPLITK=0 keeps it out of the candidate set.

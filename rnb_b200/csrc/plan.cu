@@ -249,9 +249,14 @@ bool build_conv_tc_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
       if (err) *err = "conv_tc: split-K factor too large";
       return false;
     }
+  } else if (split_n >= 16) {
+    // the caller picks the channel tile (e.g. so that position tiles x channel tiles fill one wave)
+    p.block_n = round_up(split_n, 16) < kMaxBlockN ? round_up(split_n, 16) : kMaxBlockN;
+    p.n_tiles = ceil_div(np, p.block_n);
   } else {
-    // small layers: more, narrower tiles until every SM has one
-    while (m_tiles * p.n_tiles < num_sms && p.block_n > 64) {
+    // small layers: more, narrower tiles until (nearly) every SM has one -- 147 wide tiles on
+    // 148 SMs are one full wave and must not be cut into 245 narrow ones (1.65 waves)
+    while (m_tiles * p.n_tiles * 10 < num_sms * 9 && p.block_n > 64) {
       p.block_n = round_up(p.block_n, 64) - 64;
       p.n_tiles = ceil_div(np, p.block_n);
     }
