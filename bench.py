@@ -26,7 +26,7 @@ LAYER_SIZES = {'r18': [2, 2, 2, 2, 2], 'r34': [2, 3, 4, 6, 3]}  # runner form: s
 GFLOP_PER_CLIP = {'r18': 42.172, 'r34': 76.853}
 METRIC = 'R(2+1)D clips/sec (8x112x112 clips)'
 CLIP_BYTES = 8 * 3 * 112 * 112
-NCU_DRAM_BYTES_PER_CONV_LAUNCH = 50.6e6  # profiles/r01_ncu_launches_v3.md (1719.5 MB / 34 launches)
+NCU_DRAM_BYTES_PER_CONV_LAUNCH = 50.5e6  # profiles/r01_ncu_launches_v3.md (1717.8 MB / 34 launches)
 FALLBACK_PEAK_TFLOPS = 1590.0  # /opt/skills/guides/B200_PROFILING.md, used only without MEASURED_PEAKS.json
 
 
