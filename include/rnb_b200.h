@@ -7,6 +7,17 @@
  * runner made current (reference runner.py:41-45), never rely on the legacy default stream.
  * rnb_last_error() returns a human-readable message for the calling thread's last failure.
  *
+ * Entry points that DO wait on the GPU, and say so below: rnb_r2p1d_finalize (uploads),
+ * rnb_r2p1d_prepare (times candidate kernels) and rnb_r2p1d_profile.  Nothing else synchronises.
+ *
+ * Threads: a handle belongs to one host thread at a time; different threads may drive different
+ * handles and devices concurrently (per-device one-time set-up inside the library is idempotent).
+ *
+ * Device-wide side effect: while at least one finalized bf16 handle exists on a device, the library
+ * may set cudaLimitPersistingL2CacheSize on it (the convolution outputs are marked "persisting" so
+ * that the next layer finds them in L2); destroying the last handle restores the previous limit.
+ * RNB_B200_L2_PERSIST_MB=0 in the environment switches the feature off.
+ *
  * File:line citations below are into the reference tree (snuspl/rnb @ 938d079) and name the
  * reference code each entry point replaces.
  */
@@ -59,8 +70,28 @@ int rnb_r2p1d_load_param(void* handle, const char* key, const float* host_data, 
 /* (No counterpart in the reference, where torch modules hold the parameters.)  Fold BatchNorm
  * (inference statistics) and biases into per-channel scale/shift, repack the
  * weights for the tensor cores, upload everything and allocate the activation arena.  After this
- * call the handle never allocates again except when it first sees a new batch size. */
+ * call the handle allocates no device memory again (a batch size it has not seen costs a few
+ * kilobytes of host memory for its launch plan). */
 int rnb_r2p1d_finalize(void* handle);
+
+/* Choose the kernels for `batch` clips by timing the candidates of every layer on the GPU -- the
+ * counterpart of torch.backends.cudnn.benchmark = True at runner.py:25, done explicitly and ahead of
+ * the serving loop (R2P1DRunner's warm-up forwards, models/r2p1d/model.py:66-71, are where the
+ * reference pays for it).  Synchronises `stream` and overwrites the handle's activation arena; call
+ * it from the step constructor for every batch size the pipeline can produce, never inside stream
+ * capture.  RNB_B200_PLAN_CACHE=<file> stores / reuses the choices so that processes agree.
+ * rnb_r2p1d_forward on a batch size that was never prepared does NOT time anything: it derives a
+ * plan on the host from the nearest prepared size (or from fixed rules) and stays asynchronous. */
+int rnb_r2p1d_prepare(void* handle, int batch, void* stream);
+
+/* Test and sweep hook (no counterpart in the reference): pin the kernel that runs convolution `op`
+ * (0-based, as in rnb_r2p1d_op_info) when the handle is called with `batch` clips.  kind: 1 =
+ * conv_tc_kernel with a cm x cn thread-block cluster and channel tile block_n (0 = default), 2 =
+ * conv_patch_kernel (pair = 1: its CTA-pair form), 3 = conv_splitk_kernel with ks CTAs per tile and
+ * channel tile <= block_n, 4 = conv_pair_kernel with channel tile <= block_n, 5 = conv_pair_kernel
+ * in temporal-patch mode.  RNB_EINVAL if that kernel or shape does not apply to the layer. */
+int rnb_r2p1d_force_kernel(void* handle, int batch, int op, int kind, int cm, int cn, int ks,
+                           int block_n, int pair);
 
 /* One forward pass over `batch` clips.  `in`/`out` are device pointers.
  *   in_fmt : U8_NTCHW (only when start_idx == 1; fuses the loader's float()+permute of
@@ -103,7 +134,7 @@ int rnb_r2p1d_num_convs(void* handle);
  * activations in the handle's dtype; weights are per batch and reported separately), and which
  * kernel the launch plan of the most recent batch size runs it with (before the first forward: the
  * kernel that applies): 0 = fp32 direct convolution, 1 = conv_tc_kernel, 2 = conv_patch_kernel,
- * 3 = conv_splitk_kernel, 4 = conv_pair_kernel. */
+ * 3 = conv_splitk_kernel, 4 = conv_pair_kernel, 5 = conv_pair_kernel in temporal-patch mode. */
 int rnb_r2p1d_profile(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
                       void* stream, float* ms, int cap);
 int rnb_r2p1d_op_info(void* handle, int op, char* name, int name_cap, double* flops_per_clip,
@@ -166,16 +197,28 @@ int rnb_pool_fc_classify_static(const void* x, int batch, int positions, int cha
 int rnb_batch_gather(const void* const* srcs, const int* rows, int k, void* dst, size_t row_bytes,
                      void* stream);
 
-/* sum[j] = sum over rows of logits[r][j] (optional, may be NULL) and cls = argmax_j sum[j], lowest
- * index on ties.  Replaces tensor.cpu().numpy().sum(axis=0) / .argmax() at
- * models/r2p1d/model.py:254,259,278. */
+/* sum[j] = sum over rows of logits[r][j] (optional, may be NULL) and cls = argmax_j sum[j] with
+ * numpy's rules: lowest index on ties, and a NaN sum counts as the maximum (the first NaN wins).
+ * The same rules hold for rnb_r2p1d_classify and rnb_pool_fc_classify.  Replaces
+ * tensor.cpu().numpy().sum(axis=0) / .argmax() at models/r2p1d/model.py:254,259,278. */
 int rnb_logits_sum_argmax(const float* logits, int rows, int classes, float* sum, int* cls,
                           void* stream);
 
-/* Copy `bytes` from src on device src_dev to dst on device dst_dev (NVLink peer copy when they
- * differ), ordered on `stream`.  Replaces placeholder[:n].copy_(shared[:n]) at runner.py:112-113
- * and shared[:n].copy_(segment) at runner.py:170. */
+/* Copy `bytes` from src on device src_dev to dst on device dst_dev, ordered on `stream` ONLY: the
+ * caller guarantees that whatever produced `src` has completed or is ordered before `stream`
+ * (RnB's runner synchronises its stream before it publishes, runner.py:127-128).  When the devices
+ * differ, direct peer access is enabled once per pair so that the bytes travel over NVLink; pairs
+ * that cannot reach each other fail with RNB_ECUDA.  Replaces
+ * placeholder[:n].copy_(shared[:n]) at runner.py:112-113 and shared[:n].copy_(segment) at
+ * runner.py:170. */
 int rnb_peer_copy(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes, void* stream);
+
+/* Same copy, also ordered after everything queued so far on `src_stream` (a stream of src_dev, the
+ * producer's): an event recorded there is waited for by `copy_stream` on the GPU, the host never
+ * blocks.  This is the ordering Tensor.copy_ gives the reference at runner.py:112-113,170 (it
+ * synchronises both devices' current streams) without the host-side wait. */
+int rnb_peer_copy_fenced(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes,
+                         void* src_stream, void* copy_stream);
 
 const char* rnb_last_error(void);
 

@@ -33,6 +33,8 @@ PROTOTYPES = {
     'rnb_r2p1d_forward': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                          ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                          ctypes.c_void_p]),
+    'rnb_r2p1d_prepare': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),
+    'rnb_r2p1d_force_kernel': (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 8),
     'rnb_r2p1d_classify': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                           ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                           ctypes.c_void_p, ctypes.c_void_p]),
@@ -66,6 +68,9 @@ PROTOTYPES = {
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     'rnb_peer_copy': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                      ctypes.c_size_t, ctypes.c_void_p]),
+    'rnb_peer_copy_fenced': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                            ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p,
+                                            ctypes.c_void_p]),
     'rnb_last_error': (ctypes.c_char_p, []),
 }
 

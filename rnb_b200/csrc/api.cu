@@ -1,4 +1,5 @@
 // extern "C" surface of librnb_b200.so (declared in include/rnb_b200.h).
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -96,6 +97,31 @@ int rnb_r2p1d_forward(void* handle, const void* in, int in_fmt, int batch, void*
   std::string err;
   const int rc = static_cast<rnb::R2P1DModel*>(handle)->forward(
       in, in_fmt, batch, out, out_fmt, static_cast<cudaStream_t>(stream), &err);
+  if (rc != RNB_OK) {
+    (void)cudaGetLastError();
+    return fail(rc, err);
+  }
+  return RNB_OK;
+}
+
+int rnb_r2p1d_prepare(void* handle, int batch, void* stream) {
+  if (!handle) return fail(RNB_EINVAL, "handle is NULL");
+  std::string err;
+  const int rc = static_cast<rnb::R2P1DModel*>(handle)->prepare(
+      batch, static_cast<cudaStream_t>(stream), &err);
+  if (rc != RNB_OK) {
+    (void)cudaGetLastError();
+    return fail(rc, err);
+  }
+  return RNB_OK;
+}
+
+int rnb_r2p1d_force_kernel(void* handle, int batch, int op, int kind, int cm, int cn, int ks,
+                           int block_n, int pair) {
+  if (!handle) return fail(RNB_EINVAL, "handle is NULL");
+  std::string err;
+  const int rc = static_cast<rnb::R2P1DModel*>(handle)->force_kernel(batch, op, kind, cm, cn, ks,
+                                                                      block_n, pair, &err);
   if (rc != RNB_OK) {
     (void)cudaGetLastError();
     return fail(rc, err);
@@ -262,16 +288,90 @@ int rnb_logits_sum_argmax(const float* logits, int rows, int classes, float* sum
   return RNB_OK;
 }
 
-int rnb_peer_copy(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes,
-                  void* stream) {
+namespace {
+// Direct peer access between two devices, enabled once per ordered pair.  cudaMemcpyPeerAsync works
+// without it (the driver then stages the copy through host memory); with it the copy engine moves
+// the bytes over NVLink.  Returns cudaSuccess, or the error that says the pair is not reachable.
+cudaError_t ensure_peer_access(int from_dev, int to_dev) {
+  constexpr int kMax = 64;
+  static std::atomic<int> state[kMax][kMax] = {};  // 0 unknown, 1 enabled, 2 not reachable
+  if (from_dev < 0 || to_dev < 0 || from_dev >= kMax || to_dev >= kMax) return cudaErrorInvalidDevice;
+  const int st = state[from_dev][to_dev].load();
+  if (st == 1) return cudaSuccess;
+  if (st == 2) return cudaErrorPeerAccessUnsupported;
+  int can = 0;
+  cudaError_t e = cudaDeviceCanAccessPeer(&can, from_dev, to_dev);
+  if (e != cudaSuccess) return e;
+  if (!can) {
+    state[from_dev][to_dev].store(2);
+    return cudaErrorPeerAccessUnsupported;
+  }
+  int cur = 0;
+  e = cudaGetDevice(&cur);
+  if (e != cudaSuccess) return e;
+  if (cur != from_dev) e = cudaSetDevice(from_dev);
+  if (e == cudaSuccess) {
+    e = cudaDeviceEnablePeerAccess(to_dev, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) {
+      (void)cudaGetLastError();
+      e = cudaSuccess;
+    }
+  }
+  if (cur != from_dev) (void)cudaSetDevice(cur);
+  if (e == cudaSuccess) state[from_dev][to_dev].store(1);
+  return e;
+}
+
+int peer_copy_impl(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes,
+                   cudaStream_t src_stream, bool fence_src, cudaStream_t copy_stream,
+                   const char* what) {
   if (bytes == 0) return RNB_OK;
   if (!dst || !src) return fail(RNB_EINVAL, "null pointer");
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
-  cudaError_t e = (dst_dev == src_dev)
-                      ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, s)
-                      : cudaMemcpyPeerAsync(dst, dst_dev, src, src_dev, bytes, s);
-  if (e != cudaSuccess) return cuda_fail(e, "rnb_peer_copy");
+  cudaError_t e = cudaSuccess;
+  if (dst_dev != src_dev) {
+    // both directions: the copy engine of either device may be the one that moves the bytes
+    e = ensure_peer_access(dst_dev, src_dev);
+    if (e == cudaSuccess) e = ensure_peer_access(src_dev, dst_dev);
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      return fail(RNB_ECUDA, std::string(what) + ": devices " + std::to_string(src_dev) + " and " +
+                                 std::to_string(dst_dev) +
+                                 " cannot reach each other's memory directly: " +
+                                 cudaGetErrorString(e));
+    }
+  }
+  if (fence_src && src_stream != copy_stream) {
+    // order the copy after the work that produced `src`: an event on the producer's stream (created
+    // on the producer's device) that the copy stream waits for on the GPU -- no host wait
+    int cur = 0;
+    e = cudaGetDevice(&cur);
+    if (e != cudaSuccess) return cuda_fail(e, what);
+    if (cur != src_dev) e = cudaSetDevice(src_dev);
+    cudaEvent_t ev = nullptr;
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventRecord(ev, src_stream);
+    if (cur != src_dev) (void)cudaSetDevice(cur);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(copy_stream, ev, 0);
+    if (ev) (void)cudaEventDestroy(ev);  // released once the recorded work has completed
+    if (e != cudaSuccess) return cuda_fail(e, what);
+  }
+  e = (dst_dev == src_dev) ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, copy_stream)
+                           : cudaMemcpyPeerAsync(dst, dst_dev, src, src_dev, bytes, copy_stream);
+  if (e != cudaSuccess) return cuda_fail(e, what);
   return RNB_OK;
+}
+}  // namespace
+
+int rnb_peer_copy(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes,
+                  void* stream) {
+  return peer_copy_impl(dst, dst_dev, src, src_dev, bytes, nullptr, false,
+                        static_cast<cudaStream_t>(stream), "rnb_peer_copy");
+}
+
+int rnb_peer_copy_fenced(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes,
+                         void* src_stream, void* copy_stream) {
+  return peer_copy_impl(dst, dst_dev, src, src_dev, bytes, static_cast<cudaStream_t>(src_stream),
+                        true, static_cast<cudaStream_t>(copy_stream), "rnb_peer_copy_fenced");
 }
 
 }  // extern "C"

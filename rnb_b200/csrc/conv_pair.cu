@@ -14,6 +14,7 @@
 //   warps 2-9 (both)    epilogue of the CTA's own 128 accumulator rows (its own TMEM), shared with
 //                       the other kernels (epilogue.cuh); one arrival per CTA hands the accumulator
 //                       buffer back to the leader
+#include <atomic>
 #include <stdio.h>
 
 #include "conv_tc.cuh"
@@ -342,7 +343,7 @@ conv_pair_kernel(const __grid_constant__ ConvTcParams p) {
 namespace {
 template <bool kRes, bool kRelu>
 cudaError_t launch_pair_variant(const ConvTcParams& p, int num_sms, int smem, cudaStream_t stream) {
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
@@ -367,7 +368,7 @@ cudaError_t launch_pair_variant(const ConvTcParams& p, int num_sms, int smem, cu
   cfg.attrs = attr;
   cfg.numAttrs = 2;
   // a persistent grid must be fully resident; not every SM has a partner for a 2-CTA cluster
-  static int cached[64] = {};
+  static std::atomic<int> cached[64] = {};
   int max_pairs = num_sms / 2;
   if (dev >= 0 && dev < 64) {
     if (cached[dev] == 0) {

@@ -11,6 +11,7 @@
 //               waiting with one lane + __syncwarp, costs ~120-146 cycles of R2UR traffic per MMA
 //               against 72 cycles of tensor time at N=144 (profiles/r01_mma_issue_notes.md).
 //   warps 2-9   epilogue: tcgen05.ld -> +shift (+residual) -> ReLU -> bf16 -> 32-byte global stores
+#include <atomic>
 #include <stdio.h>
 
 #include "conv_patch.cuh"
@@ -549,7 +550,7 @@ namespace {
 template <bool kRes, bool kRelu, bool kStream, bool kPair>
 cudaError_t launch_patch_variant(const ConvPatchParams& p, int num_sms, int smem,
                                  cudaStream_t stream) {
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
@@ -580,7 +581,7 @@ cudaError_t launch_patch_variant(const ConvPatchParams& p, int num_sms, int smem
     cfg.numAttrs = 2;
     // A persistent grid must be fully resident.  Not every SM has a partner for a 2-CTA cluster
     // (SMs fused off leave single-SM TPCs), so ask how many pairs fit at once.
-    static int cached[64] = {};
+    static std::atomic<int> cached[64] = {};
     if (dev >= 0 && dev < 64 && cached[dev] == 0) {
       cfg.gridDim = dim3(2 * (num_sms / 2));
       int n = 0;

@@ -17,6 +17,7 @@
 // The summation order over the K ranges is fixed (rank 0, 1, ...), so results are deterministic.
 // Roles and pipeline are those of conv_tc.cu: warp 0 TMA producer, warp 1 MMA issuer, warps 2-9
 // epilogue; all 320 threads take part in the two cluster barriers of every work item.
+#include <atomic>
 #include <stdio.h>
 
 #include "conv_tc.cuh"
@@ -264,7 +265,7 @@ conv_splitk_kernel(const __grid_constant__ ConvTcParams p) {
 namespace {
 template <bool kRes, bool kRelu>
 cudaError_t launch_sk_variant(const ConvTcParams& p, int num_sms, int smem, cudaStream_t stream) {
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
@@ -289,7 +290,7 @@ cudaError_t launch_sk_variant(const ConvTcParams& p, int num_sms, int smem, cuda
   cfg.attrs = attr;
   cfg.numAttrs = 2;
   // how many clusters of this size the device can hold at once (GPC boundaries strand SMs)
-  static int cached[64][kMaxSplitK + 1] = {};
+  static std::atomic<int> cached[64][kMaxSplitK + 1] = {};
   int max_clusters = num_sms / p.ks;
   if (dev >= 0 && dev < 64) {
     if (cached[dev][p.ks] == 0) {

@@ -11,6 +11,7 @@
 //   warps 2-9   epilogue: tcgen05.ld the accumulator (lane == output position), folded BatchNorm /
 //               bias (shift; the scale lives in the weights), optional residual add and ReLU, bf16
 //               pack, one 32-byte global store per 16 channels (rows outside the tensor masked).
+#include <atomic>
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -330,7 +331,7 @@ conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
 namespace {
 template <bool kRes, bool kRelu>
 cudaError_t launch_variant(const ConvTcParams& p, int num_sms, int smem, cudaStream_t stream) {
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
@@ -359,7 +360,7 @@ cudaError_t launch_variant(const ConvTcParams& p, int num_sms, int smem, cudaStr
     attr[1].val.clusterDim.z = 1;
     cfg.numAttrs = 2;
     // how many clusters of this shape the device can hold at once (GPC boundaries strand SMs)
-    static int cached[64][5] = {};
+    static std::atomic<int> cached[64][5] = {};
     if (dev >= 0 && dev < 64 && cached[dev][csize] == 0) {
       cfg.gridDim = dim3(csize * (num_sms / csize));
       int n = 0;
@@ -383,6 +384,9 @@ struct L2PersistState {
   size_t max_carve = 0;  // what the device (and RNB_B200_L2_PERSIST_MB) allow
   size_t carve = 0;      // current cudaLimitPersistingL2CacheSize set by this library (0 = off)
   int max_window = 0;
+  size_t prev_limit = 0;  // the device's limit before this library first changed it
+  bool touched = false;
+  int users = 0;          // finalized model handles on this device
 };
 L2PersistState g_l2[64];
 
@@ -415,8 +419,29 @@ void l2_persist_configure(size_t largest_tensor_bytes) {
   // batch 32, -19 % at batch 64 with the carve-out left on): measured crossover ~1.5x.
   const size_t want = (double)largest_tensor_bytes <= 1.5 * (double)st->max_carve ? st->max_carve : 0;
   if (want == st->carve) return;
+  if (!st->touched) {
+    // remembered so that the last handle's destruction can put the device-wide limit back
+    if (cudaDeviceGetLimit(&st->prev_limit, cudaLimitPersistingL2CacheSize) != cudaSuccess)
+      st->prev_limit = 0;
+    st->touched = true;
+  }
   if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) st->carve = want;
   (void)cudaGetLastError();
+}
+
+void l2_persist_acquire() {
+  if (L2PersistState* st = l2_state()) ++st->users;
+}
+
+void l2_persist_release() {
+  L2PersistState* st = l2_state();
+  if (!st || st->users <= 0) return;
+  if (--st->users == 0 && st->touched) {
+    (void)cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, st->prev_limit);
+    (void)cudaGetLastError();
+    st->carve = 0;
+    st->touched = false;
+  }
 }
 
 int add_l2_output_window(cudaLaunchAttribute* attr, int n, const void* ptr, size_t bytes) {

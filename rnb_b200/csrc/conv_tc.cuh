@@ -84,7 +84,12 @@ cudaError_t launch_conv_tc(const ConvTcParams& p, int num_sms, cudaStream_t stre
 // tensor of the forward mostly fits it, and zero otherwise: l2_persist_configure(), called before
 // the launches of a forward, switches it when the batch size changes regime.
 // add_l2_output_window appends the attribute to attr[n] and returns the new count.
+// cudaLimitPersistingL2CacheSize is a DEVICE-WIDE setting shared with every other stream and
+// library in the context: l2_persist_acquire / _release count the model handles alive on the
+// current device, and the last release puts back the limit found before the first change.
 void l2_persist_configure(size_t largest_tensor_bytes);
+void l2_persist_acquire();
+void l2_persist_release();
 int add_l2_output_window(cudaLaunchAttribute* attr, int n, const void* ptr, size_t bytes);
 
 // Split-K variant: the fp32 staging area of the reduction (block_n x 128) aliases the operand ring.

@@ -4,6 +4,7 @@
 
 #include <stdio.h>
 
+#include <atomic>
 #include <utility>
 
 #include "conv_tc.cuh"
@@ -16,11 +17,11 @@ namespace {
 // previous kernel in the stream drains (its prologue overlaps that tail; measured 0.9 us instead
 // of 4.1 us between kernels on a B200) and must execute griddepcontrol.wait before it touches
 // anything the previous kernel reads or writes.
-const void* g_pdl_window_ptr = nullptr;  // output of the next launch_pdl (L2 persistence), if any
-size_t g_pdl_window_bytes = 0;
+// `win_ptr` / `win_bytes`: the launch's output tensor for the L2 persistence window (conv_tc.cuh),
+// or nullptr / 0.
 template <typename... KArgs, typename... Args>
 cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
-                       Args&&... args) {
+                       const void* win_ptr, size_t win_bytes, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -30,9 +31,7 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = add_l2_output_window(attr, 1, g_pdl_window_ptr, g_pdl_window_bytes);
-  g_pdl_window_ptr = nullptr;
-  g_pdl_window_bytes = 0;
+  cfg.numAttrs = add_l2_output_window(attr, 1, win_ptr, win_bytes);
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 }  // namespace
@@ -41,6 +40,15 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
 namespace {
 
 constexpr int kThreads = 256;
+
+// arg-max order of numpy (reference models/r2p1d/model.py:259,278): NaN counts as the maximum, and
+// among equal candidates (or several NaNs) the lowest index wins.  True when (v, i) beats (bv, bi).
+__device__ __forceinline__ bool argmax_takes(float v, int i, float bv, int bi) {
+  const bool vn = v != v, bn = bv != bv;
+  if (vn != bn) return vn;
+  if (vn) return i < bi;
+  return v > bv || (v == bv && i < bi);
+}
 
 inline int blocks_for(long long n, int threads = kThreads) {
   long long b = (n + threads - 1) / threads;
@@ -377,7 +385,7 @@ pool_fc_classify_kernel(const In* __restrict__ x, int S, int C, const float* __r
     float acc = 0.f;
     for (int b = 0; b < B; ++b) acc += __ldcg(staged + (long long)b * num_classes + j);
     if (sum) sum[j] = acc;
-    if (acc > bv || (acc == bv && j < bi)) {
+    if (argmax_takes(acc, j, bv, bi)) {
       bv = acc;
       bi = j;
     }
@@ -386,7 +394,7 @@ pool_fc_classify_kernel(const In* __restrict__ x, int S, int C, const float* __r
   for (int off = 16; off > 0; off >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, bv, off);
     const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-    if (ov > bv || (ov == bv && oi < bi)) {
+    if (argmax_takes(ov, oi, bv, bi)) {
       bv = ov;
       bi = oi;
     }
@@ -399,7 +407,7 @@ pool_fc_classify_kernel(const In* __restrict__ x, int S, int C, const float* __r
   __syncthreads();
   if (threadIdx.x == 0) {
     for (int k = 1; k < (int)(blockDim.x >> 5); ++k)
-      if (best_v[k] > bv || (best_v[k] == bv && best_i[k] < bi)) {
+      if (argmax_takes(best_v[k], best_i[k], bv, bi)) {
         bv = best_v[k];
         bi = best_i[k];
       }
@@ -437,7 +445,7 @@ __global__ void sum_argmax_kernel(const float* __restrict__ logits, int rows, in
     float acc = 0.f;
     for (int r = 0; r < rows; ++r) acc += logits[(long long)r * classes + j];
     if (sum) sum[j] = acc;
-    if (acc > bv || (acc == bv && j < bi)) {
+    if (argmax_takes(acc, j, bv, bi)) {
       bv = acc;
       bi = j;
     }
@@ -446,7 +454,7 @@ __global__ void sum_argmax_kernel(const float* __restrict__ logits, int rows, in
   for (int off = 16; off > 0; off >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, bv, off);
     const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-    if (ov > bv || (ov == bv && oi < bi)) {
+    if (argmax_takes(ov, oi, bv, bi)) {
       bv = ov;
       bi = oi;
     }
@@ -465,7 +473,7 @@ __global__ void sum_argmax_kernel(const float* __restrict__ logits, int rows, in
     for (int off = 16; off > 0; off >>= 1) {
       const float ov = __shfl_xor_sync(0xffffffffu, bv, off);
       const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-      if (ov > bv || (ov == bv && oi < bi)) {
+      if (argmax_takes(ov, oi, bv, bi)) {
         bv = ov;
         bi = oi;
       }
@@ -488,10 +496,8 @@ cudaError_t launch_pre_u8_to_stem(const uint8_t* in, int batch, const float* sca
                                   const float* bias3, __nv_bfloat16* out, cudaStream_t s) {
   const int rows = batch * kClipT * kClipH;
   if (rows == 0) return cudaSuccess;
-  g_pdl_window_ptr = out;
-  g_pdl_window_bytes = (size_t)rows * (kClipW / 2) * kStemUnfold * 2;
   return launch_pdl(to_stem_kernel<uint8_t>, dim3((rows + kStemRows - 1) / kStemRows), dim3(256), 0,
-                    s, in, rows, make_affine(scale3, bias3), reinterpret_cast<uint4*>(out), false);
+                    s, out, (size_t)rows * (kClipW / 2) * kStemUnfold * 2, in, rows, make_affine(scale3, bias3), reinterpret_cast<uint4*>(out), false);
 }
 
 cudaError_t launch_f32_ncdhw_to_stem(const float* in, int batch, __nv_bfloat16* out,
@@ -499,7 +505,7 @@ cudaError_t launch_f32_ncdhw_to_stem(const float* in, int batch, __nv_bfloat16* 
   const int rows = batch * kClipT * kClipH;
   if (rows == 0) return cudaSuccess;
   return launch_pdl(to_stem_kernel<float>, dim3((rows + kStemRows - 1) / kStemRows), dim3(256), 0, s,
-                    in, rows, make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
+                    nullptr, 0, in, rows, make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
 }
 
 cudaError_t launch_pre_u8_to_f32_ncdhw(const uint8_t* in, int batch, const float* scale3,
@@ -571,14 +577,14 @@ cudaError_t launch_pool_fc_bf16(const __nv_bfloat16* x, int B, int S, int C, con
                                 cudaStream_t s) {
   if (B == 0) return cudaSuccess;
   return launch_pdl(pool_fc_kernel<__nv_bfloat16>, dim3(B, pool_fc_chunks(num_classes)),
-                    dim3(kPoolThreads), pool_fc_smem_bytes(C), s, x, S, C, w, bias, num_classes,
-                    logits);
+                    dim3(kPoolThreads), pool_fc_smem_bytes(C), s, nullptr, 0, x, S, C, w, bias,
+                    num_classes, logits);
 }
 cudaError_t launch_pool_fc_f32(const float* x, int B, int S, int C, const float* w,
                                const float* bias, int num_classes, float* logits, cudaStream_t s) {
   if (B == 0) return cudaSuccess;
   return launch_pdl(pool_fc_kernel<float>, dim3(B, pool_fc_chunks(num_classes)), dim3(kPoolThreads),
-                    pool_fc_smem_bytes(C), s, x, S, C, w, bias, num_classes, logits);
+                    pool_fc_smem_bytes(C), s, nullptr, 0, x, S, C, w, bias, num_classes, logits);
 }
 
 size_t pool_fc_classify_scratch_bytes(int batch, int num_classes) {
@@ -609,19 +615,20 @@ static __device__ __align__(256) unsigned char g_static_classify_scratch[kStatic
 
 cudaError_t static_classify_scratch(void** ptr) {
   constexpr int kMaxDevices = 64;
-  static void* resolved[kMaxDevices] = {};
+  // (atomic: two host threads making the first call on one device both resolve the same address)
+  static std::atomic<void*> resolved[kMaxDevices] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
-  if (resolved[dev] == nullptr) {
+  if (resolved[dev].load() == nullptr) {
     // set-up, once per device, with that device current: every GPU has its own copy of the array
     void* p = nullptr;
     e = cudaGetSymbolAddress(&p, g_static_classify_scratch);
     if (e != cudaSuccess) return e;
-    resolved[dev] = p;
+    resolved[dev].store(p);
   }
-  *ptr = resolved[dev];
+  *ptr = resolved[dev].load();
   return cudaSuccess;
 }
 

@@ -56,6 +56,16 @@ R2P1DModel::R2P1DModel(std::vector<int> layer_sizes, int start_idx, int end_idx,
 R2P1DModel::~R2P1DModel() { release(); }
 
 void R2P1DModel::release() {
+  if (finalized_) {
+    // (the L2 carve-out is a device-wide limit: the last handle on the device puts it back)
+    int cur = 0;
+    if (cudaGetDevice(&cur) == cudaSuccess) {
+      if (cur != device_) cudaSetDevice(device_);
+      l2_persist_release();
+      if (cur != device_) cudaSetDevice(cur);
+    }
+    finalized_ = false;
+  }
   for (ConvOp& op : ops_) {
     if (op.d_w) cudaFree(op.d_w);
     if (op.d_scale) cudaFree(op.d_scale);
@@ -362,6 +372,7 @@ int R2P1DModel::finalize(std::string* err) {
   }
   params_.clear();
   finalized_ = true;
+  l2_persist_acquire();
   return RNB_OK;
 }
 
@@ -406,7 +417,7 @@ bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
     if (dtype_ == RNB_DTYPE_BF16 && it != plans_.end())
       for (const Launch& l : it->second)
         if (l.op == op) {
-          kind = l.patch ? 2 : (l.tc.pair ? 4 : (l.tc.ks > 1 ? 3 : 1));
+          kind = l.patch ? 2 : (l.tc.pair ? (l.tc.tpatch ? 5 : 4) : (l.tc.ks > 1 ? 3 : 1));
           break;
         }
     *kernel_kind = kind;
@@ -430,7 +441,7 @@ int R2P1DModel::profile(const void* in, int in_fmt, int batch, void* out, int ou
   // one event per kernel; a chunked convolution's launches are summed into its entry
   std::vector<int> launch_op;
   if (dtype_ == RNB_DTYPE_BF16 && batch > 0 && batch <= max_batch_) {
-    const std::vector<Launch>* plan = ensure_plan(batch, stream, err);
+    const std::vector<Launch>* plan = ensure_plan(batch, stream, err, false);
     last_batch_ = batch;
     if (!plan) return RNB_ECUDA;
     for (const Launch& l : *plan) launch_op.push_back(l.op);
@@ -465,7 +476,7 @@ int R2P1DModel::profile(const void* in, int in_fmt, int batch, void* out, int ou
 // fastest depends on the layer (shared-memory bandwidth vs. tile fit vs. lock-step between CTAs),
 // and the reference runs with cudnn.benchmark = True for the same reason (runner.py:25).
 bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cudaStream_t stream,
-                           const Launch* like, Launch* out, std::string* err) {
+                           const Launch* like, Launch* out, std::string* err, bool tune) {
   const ConvOp& op = ops_[op_index];
   // a chunked spatial->temporal pair reuses the START of the intermediate slot for every chunk
   const size_t in_off = (chunked && op.in_slot == SLOT_M) ? 0 : (size_t)first * op.g.in_elems(1);
@@ -492,7 +503,7 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
     out->patch = like->patch;
     const bool ok = like->patch
                         ? build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
-                                                  &out->pp, &perr)
+                                                  &out->pp, &perr, like->pp.pair)
                     : like->tc.tpatch
                         ? build_conv_tpatch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu,
                                                    like->tc.block_n, &out->tc, &perr)
@@ -511,6 +522,15 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
   if (patch_only) {
     out->patch = true;
     return build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &out->pp, &perr)
+               ? true
+               : fail(perr);
+  }
+  if (!tune) {
+    // no timing (a batch size nobody prepared): the tap kernel with the traffic model's cluster
+    // shape runs every geometry; host work only
+    out->patch = false;
+    return build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &out->tc,
+                                &perr, 0, 0, 0, 0, 0, xe)
                ? true
                : fail(perr);
   }
@@ -796,6 +816,7 @@ bool R2P1DModel::load_cached_plan(const char* path, int batch, cudaStream_t stre
       like.tc.ks = ks;
       like.tc.block_n = bn;
       like.tc.pair = pair;
+      like.pp.pair = pair;
       like.tc.tpatch = tpatch;
       std::string e;
       if (!plan_conv(i, 0, batch, false, stream, &like, &l, &e)) found = false;
@@ -815,23 +836,112 @@ void R2P1DModel::save_cached_plan(const char* path, int batch, const std::vector
   fprintf(f, "plan %llx %d\n", (unsigned long long)plan_key(batch), (int)plan.size());
   for (const Launch& l : plan)
     fprintf(f, "%d %d %d %d %d %d %d %d\n", l.op, l.patch ? 1 : 0, l.tc.cm, l.tc.cn, l.tc.ks,
-            l.tc.block_n, l.tc.pair, l.tc.tpatch);
+            l.tc.block_n, l.patch ? l.pp.pair : l.tc.pair, l.tc.tpatch);
   fclose(f);
 }
 
+// The plan of a batch size nobody prepared, built WITHOUT timing and without touching the GPU: every
+// layer copies the kernel choice of the nearest prepared batch size (cluster shapes and split-K
+// factors that do not apply at this size fall back to the plain tap kernel); with nothing prepared
+// yet, the patch kernel where it keeps its weights resident and the tap kernel elsewhere.
+bool R2P1DModel::derive_plan(int batch, std::vector<Launch>* plan, std::string* err) {
+  const std::vector<Launch>* src = nullptr;
+  double best = 0;
+  for (int b : tuned_) {
+    const auto it = plans_.find(b);
+    if (it == plans_.end() || it->second.size() != ops_.size()) continue;  // chunked schedules
+    const double d = fabs(log((double)b / (double)batch));
+    if (!src || d < best) {
+      src = &it->second;
+      best = d;
+    }
+  }
+  for (int i = 0; i < (int)ops_.size(); ++i) {
+    Launch l;
+    std::string e;
+    if (!(src && plan_conv(i, 0, batch, false, nullptr, &(*src)[i], &l, &e)) &&
+        !plan_conv(i, 0, batch, false, nullptr, nullptr, &l, err, false))
+      return false;
+    plan->push_back(l);
+  }
+  return true;
+}
+
 const std::vector<R2P1DModel::Launch>* R2P1DModel::ensure_plan(int batch, cudaStream_t stream,
-                                                               std::string* err) {
+                                                               std::string* err, bool tune) {
   auto it = plans_.find(batch);
-  if (it == plans_.end()) {
-    std::vector<Launch> plan;
+  if (it != plans_.end() && (!tune || tuned_.count(batch))) return &it->second;
+  std::vector<Launch> plan;
+  if (tune) {
     const char* cache = getenv("RNB_B200_PLAN_CACHE");
     if (!(cache && cache[0] && load_cached_plan(cache, batch, stream, &plan))) {
       if (!build_plan(batch, stream, &plan, err)) return nullptr;
       if (cache && cache[0]) save_cached_plan(cache, batch, plan);
     }
-    it = plans_.emplace(batch, std::move(plan)).first;
+    tuned_.insert(batch);
+  } else if (!derive_plan(batch, &plan, err)) {
+    return nullptr;
   }
-  return &it->second;
+  plans_[batch] = std::move(plan);
+  return &plans_[batch];
+}
+
+int R2P1DModel::prepare(int batch, cudaStream_t stream, std::string* err) {
+  if (!finalized_) {
+    if (err) *err = "prepare before finalize";
+    return RNB_ESTATE;
+  }
+  if (batch < 1 || batch > max_batch_) {
+    if (err)
+      *err = "batch " + std::to_string(batch) + " outside [1, max_batch = " +
+             std::to_string(max_batch_) + "]";
+    return RNB_EINVAL;
+  }
+  if (dtype_ != RNB_DTYPE_BF16) return RNB_OK;  // the fp32 parity mode has one kernel
+  return ensure_plan(batch, stream, err, true) ? RNB_OK : RNB_ECUDA;
+}
+
+int R2P1DModel::force_kernel(int batch, int op_index, int kind, int cm, int cn, int ks, int block_n,
+                             int pair, std::string* err) {
+  if (!finalized_ || dtype_ != RNB_DTYPE_BF16) {
+    if (err) *err = "force_kernel needs a finalized bf16 handle";
+    return RNB_ESTATE;
+  }
+  if (batch < 1 || batch > max_batch_ || op_index < 0 || op_index >= (int)ops_.size()) {
+    if (err) *err = "force_kernel: batch or op index out of range";
+    return RNB_EINVAL;
+  }
+  if (!ensure_plan(batch, nullptr, err, false)) return RNB_ECUDA;
+  std::vector<Launch>& plan = plans_[batch];
+  if (plan.size() != ops_.size()) {
+    if (err) *err = "force_kernel: chunked schedules cannot be edited";
+    return RNB_ESTATE;
+  }
+  Launch like, l;
+  switch (kind) {
+    case 1: like.tc.cm = cm > 0 ? cm : 1; like.tc.cn = cn > 0 ? cn : 1; like.tc.block_n = block_n; break;
+    case 2: like.patch = true; like.pp.pair = pair ? 1 : 0; break;
+    case 3: like.tc.ks = ks; like.tc.block_n = block_n; break;
+    case 4: like.tc.pair = 1; like.tc.block_n = block_n; break;
+    case 5: like.tc.pair = 1; like.tc.tpatch = 1; like.tc.block_n = block_n; break;
+    default:
+      if (err) *err = "force_kernel: unknown kernel kind " + std::to_string(kind);
+      return RNB_EINVAL;
+  }
+  if (!plan_conv(op_index, 0, batch, false, nullptr, &like, &l, err)) return RNB_EINVAL;
+  // the builders fall back silently where a shape does not apply: report that as an error here
+  const bool ok = kind == 1   ? (!l.patch && l.tc.cm == like.tc.cm && l.tc.cn == like.tc.cn &&
+                                 l.tc.ks <= 1 && !l.tc.pair)
+                  : kind == 2 ? (l.patch && l.pp.pair == like.pp.pair)
+                  : kind == 3 ? (!l.patch && l.tc.ks == ks && ks > 1)
+                  : kind == 4 ? (!l.patch && l.tc.pair && !l.tc.tpatch)
+                              : (!l.patch && l.tc.pair && l.tc.tpatch);
+  if (!ok) {
+    if (err) *err = ops_[op_index].name + ": the requested kernel shape does not apply to this layer";
+    return RNB_EINVAL;
+  }
+  plan[op_index] = l;
+  return RNB_OK;
 }
 
 int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int out_fmt,
@@ -867,11 +977,13 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
     if (err) *err = "unsupported output format " + std::to_string(out_fmt) + " for this handle";
     return RNB_EINVAL;
   }
-  // ---- launch plan for this batch size (first use only).  Built BEFORE the input is staged:
-  // tuning launches the convolutions on whatever the arena holds and overwrites every slot.
+  // ---- launch plan for this batch size: what prepare() timed, or -- for a size nobody prepared --
+  // a plan derived on the host from the nearest prepared size (no timing, no synchronisation).
+  // (Every TMA tensor map of a plan covers only this handle's own arena and weights, allocated on
+  // this device; caller pointers are read by the staging kernels / copies below, never by TMA.)
   const std::vector<Launch>* plan = nullptr;
   if (tc) {
-    plan = ensure_plan(batch, stream, err);
+    plan = ensure_plan(batch, stream, err, false);
     last_batch_ = batch;
     if (!plan) return RNB_ECUDA;
     // L2 persistence carve-out on or off for this batch size (conv_tc.cuh)

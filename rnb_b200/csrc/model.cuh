@@ -1,6 +1,7 @@
 // R(2+1)D layer-range model: op list, folded parameters, activation arena, per-batch launch plans.
 #pragma once
 #include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -52,6 +53,14 @@ class R2P1DModel {
               int* video_cls = nullptr, bool video = false);
   int profile(const void* in, int in_fmt, int batch, void* out, int out_fmt, cudaStream_t stream,
               float* ms, int cap, std::string* err);
+  // Times the candidate kernels of every layer at `batch` clips and keeps the fastest (the launch
+  // plan of that batch size).  Synchronises `stream` and overwrites the activation arena.
+  int prepare(int batch, cudaStream_t stream, std::string* err);
+  // Pins the kernel of convolution `op` in the plan of `batch` (parity tests, sweeps): kind as in
+  // op_info (1 tap, 2 patch, 3 split-K, 4 CTA pair, 5 CTA-pair temporal patch).
+  int force_kernel(int batch, int op, int kind, int cm, int cn, int ks, int block_n, int pair,
+                   std::string* err);
+  bool plan_is_tuned(int batch) const { return tuned_.count(batch) != 0; }
   bool op_info(int op, std::string* name, double* flops_per_clip, double* act_bytes_per_clip,
                double* weight_bytes, int* kernel_kind) const;
   void io_shape(int which, int64_t shape4[4]) const;
@@ -104,14 +113,17 @@ class R2P1DModel {
     ConvPatchParams pp = {};
   };
   bool plan_conv(int op_index, int first, int batch, bool chunked, cudaStream_t stream,
-                 const Launch* like, Launch* out, std::string* err);
+                 const Launch* like, Launch* out, std::string* err, bool tune = true);
   bool build_plan(int batch, cudaStream_t stream, std::vector<Launch>* plan, std::string* err);
-  const std::vector<Launch>* ensure_plan(int batch, cudaStream_t stream, std::string* err);
+  bool derive_plan(int batch, std::vector<Launch>* plan, std::string* err);
+  const std::vector<Launch>* ensure_plan(int batch, cudaStream_t stream, std::string* err,
+                                         bool tune);
   uint64_t plan_key(int batch) const;
   bool load_cached_plan(const char* path, int batch, cudaStream_t stream, std::vector<Launch>* plan);
   void save_cached_plan(const char* path, int batch, const std::vector<Launch>& plan);
   cudaError_t launch_tc(const ConvTcParams& tc, cudaStream_t stream) const;
   std::map<int, std::vector<Launch>> plans_;  // per batch size
+  std::set<int> tuned_;                       // batch sizes whose plan was timed (or read from the cache)
   int last_batch_ = 0;                        // batch size of the most recent forward
   int last_launches_ = 0;                     // kernels launched by the most recent forward
 };

@@ -180,10 +180,35 @@ class R2P1DEngine:
     def num_convs(self):
         return int(self.lib.rnb_r2p1d_num_convs(self._handle))
 
+    def prepare(self, *batches):
+        """Time the candidate kernels for each of ``batches`` clips and keep the fastest per layer.
+
+        The explicit counterpart of ``cudnn.benchmark`` (reference runner.py:25): synchronises the
+        current stream and overwrites the engine's activation arena, so call it during set-up.  A
+        batch size that was never prepared still runs -- with a plan derived on the host from the
+        nearest prepared size -- and ``forward`` stays asynchronous either way.
+        """
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with torch.cuda.device(self.device_index):
+            for b in batches:
+                if 1 <= int(b) <= self.max_batch:
+                    _lib.check(self.lib.rnb_r2p1d_prepare(self._handle, int(b),
+                                                          ctypes.c_void_p(stream)))
+        return self
+
+    KERNEL_KINDS = ('conv_ref', 'conv_tc', 'conv_patch', 'conv_splitk', 'conv_pair', 'conv_tpatch')
+
+    def force_kernel(self, batch, op, kind, cm=0, cn=0, ks=0, block_n=0, pair=0):
+        """Pin the kernel of convolution ``op`` at ``batch`` clips (tests and sweeps).  ``kind`` is a
+        name from ``KERNEL_KINDS``; raises RnbError when it does not apply to the layer."""
+        k = self.KERNEL_KINDS.index(kind)
+        _lib.check(self.lib.rnb_r2p1d_force_kernel(self._handle, int(batch), int(op), k, cm, cn, ks,
+                                                   block_n, pair))
+
     def op_info(self):
         """[(state_dict prefix, FLOPs per clip, activation bytes per clip, weight bytes, kernel)]
-        per convolution; kernel is 'conv_ref', 'conv_tc', 'conv_patch', 'conv_splitk' or 'conv_pair' (what the
-        launch plan of the most recent batch size chose)."""
+        per convolution; kernel is one of ``KERNEL_KINDS`` (what the launch plan of the most recent
+        batch size runs)."""
         info = []
         for i in range(self.num_convs):
             name = ctypes.create_string_buffer(256)
@@ -192,7 +217,7 @@ class R2P1DEngine:
                                                   ctypes.byref(a), ctypes.byref(w),
                                                   ctypes.byref(k)))
             info.append((name.value.decode(), f.value, a.value, w.value,
-                         ('conv_ref', 'conv_tc', 'conv_patch', 'conv_splitk', 'conv_pair')[k.value]))
+                         self.KERNEL_KINDS[k.value]))
         return info
 
     def profile(self, x):
@@ -221,21 +246,49 @@ class R2P1DEngine:
             if tuple(x.shape[1:]) != self.in_shape:
                 raise ValueError('expected input (B, %s), got %s' % (self.in_shape, tuple(x.shape)))
             fmt = _lib.FMT_F32_NCDHW
+        elif x.dtype == torch.bfloat16 and self.dtype == 'bf16' and self.start_index > 1:
+            # the library's private hand-off format between layer ranges: channels last, 16-padded
+            if tuple(x.shape[1:]) != self.wire_shape(self.in_shape):
+                raise ValueError('expected bf16 input (B, %s), got %s'
+                                 % (self.wire_shape(self.in_shape), tuple(x.shape)))
+            fmt = _lib.FMT_BF16_NDHWC
         else:
-            raise TypeError('input must be uint8 frames or float32 activations, got %s' % x.dtype)
+            raise TypeError('input must be uint8 frames, float32 (B, C, T, H, W) activations or '
+                            'bf16 channels-last activations, got %s' % x.dtype)
         if not x.is_contiguous():
             x = x.contiguous()
         if batch > self.max_batch:
             raise ValueError('batch %d exceeds max_batch %d' % (batch, self.max_batch))
         return x, fmt, batch
 
-    def forward(self, x, out=None):
-        """``x``: uint8 (B, 8, 3, 112, 112) loader frames (start layer 1 only) or fp32
-        (B, C, T, H, W).  Returns fp32 (B, num_classes) logits, or fp32 (B, C, T, H, W) activations
-        when the range ends before layer 5.  The result aliases an engine-owned buffer that the
-        next call overwrites, unless ``out`` is given.  Asynchronous on the current stream.
+    @staticmethod
+    def wire_shape(cthw):
+        """Per-clip shape of the private bf16 hand-off format for a logical (C, T, H, W)."""
+        c, t, h, w = cthw
+        return (t, h, w, (c + 15) // 16 * 16)
+
+    def forward(self, x, out=None, wire=False):
+        """``x``: uint8 (B, 8, 3, 112, 112) loader frames (start layer 1 only), fp32
+        (B, C, T, H, W), or -- between two engines -- bf16 (B, T, H, W, pad16(C)).  Returns fp32
+        (B, num_classes) logits, or fp32 (B, C, T, H, W) activations when the range ends before
+        layer 5 (``wire=True``: the bf16 channels-last form instead, half the bytes and no layout
+        change on either side).  The result aliases an engine-owned buffer that the next call
+        overwrites, unless ``out`` is given.  Asynchronous on the current stream.
         """
         x, fmt, batch = self._check_input(x)
+        if wire:
+            if self.end_index == 5 or self.dtype != 'bf16':
+                raise ValueError('wire=True needs a bf16 engine that ends before layer 5')
+            if out is None:
+                if not hasattr(self, '_out_wire'):
+                    self._out_wire = torch.empty((self.max_batch,) + self.wire_shape(self.out_shape),
+                                                 dtype=torch.bfloat16, device=self.device)
+                out = self._out_wire[:batch]
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            _lib.check(self.lib.rnb_r2p1d_forward(self._handle, ctypes.c_void_p(x.data_ptr()), fmt,
+                                                  batch, ctypes.c_void_p(out.data_ptr()),
+                                                  _lib.FMT_BF16_NDHWC, ctypes.c_void_p(stream)))
+            return out
         if out is None:
             out = self._out[:batch]
         out_fmt = _lib.FMT_F32_LOGITS if self.end_index == 5 else _lib.FMT_F32_NCDHW
@@ -300,6 +353,7 @@ class HostPipeline:
         self.in_free = [torch.cuda.Event() for _ in range(depth)]
         self.out_ready = [torch.cuda.Event() for _ in range(depth)]
         self.count = 0
+        self.unread = [False] * depth  # slot holds a result the caller has not asked for yet
         self.h2d_bytes = self.dev_in[0].numel()
         self.d2h_bytes = self.host_out[0].numel() * 4
 
@@ -309,6 +363,10 @@ class HostPipeline:
         ``result(slot)`` waits for them.  At most ``depth`` batches may be outstanding.
         """
         slot = self.count % self.depth
+        if self.unread[slot]:
+            raise RuntimeError('HostPipeline: %d batches are outstanding; call result(%d) before '
+                               'submitting another one (its host buffer would be overwritten)'
+                               % (self.depth, slot))
         compute = torch.cuda.current_stream(self.engine.device)
         n = host_frames.shape[0]
         with torch.cuda.stream(self.copy_stream):
@@ -329,8 +387,12 @@ class HostPipeline:
             self.host_out[slot][:n].copy_(logits, non_blocking=True)
             self.out_ready[slot].record(self.out_stream)
         self.count += 1
+        self.unread[slot] = True
         return slot
 
     def result(self, slot):
+        """Wait for the logits of the batch submitted into ``slot``; the returned pinned tensor is
+        valid until ``depth`` more batches have been submitted."""
         self.out_ready[slot].synchronize()
+        self.unread[slot] = False
         return self.host_out[slot]

@@ -124,11 +124,14 @@ def pool_fc_classify(x, weight, bias, scratch=None, want_logits=True):
     return logits, total, cls
 
 
-def peer_copy(dst, src):
+def peer_copy(dst, src, src_stream=None, on=None):
     """``dst.copy_(src)`` for same-shape contiguous CUDA tensors, possibly on different GPUs.
 
-    Ordered on the current stream of the *destination* device (the consumer pulls, as in
-    runner.py:112-113).
+    Runs on stream ``on`` (default: the current stream of the *destination* device -- the consumer
+    pulls, as in runner.py:112-113) and is ordered, on the GPU, after everything queued so far on
+    ``src_stream`` (default: the current stream of the source device, i.e. after the kernels that
+    produced ``src``; it must be a stream of the source device).  That is the ordering
+    ``Tensor.copy_`` gives the reference, without its host wait.
     """
     lib = _lib.load()
     if dst.shape != src.shape or dst.dtype != src.dtype:
@@ -136,8 +139,13 @@ def peer_copy(dst, src):
     if not (dst.is_contiguous() and src.is_contiguous() and dst.is_cuda and src.is_cuda):
         raise ValueError('peer_copy needs contiguous CUDA tensors')
     nbytes = src.numel() * src.element_size()
-    with torch.cuda.device(dst.device):
-        _lib.check(lib.rnb_peer_copy(ctypes.c_void_p(dst.data_ptr()), dst.device.index,
-                                     ctypes.c_void_p(src.data_ptr()), src.device.index, nbytes,
-                                     _stream(dst.device)))
+    if src_stream is None:
+        src_stream = torch.cuda.current_stream(src.device)
+    if on is None:
+        on = torch.cuda.current_stream(dst.device)
+    with torch.cuda.device(on.device):
+        _lib.check(lib.rnb_peer_copy_fenced(ctypes.c_void_p(dst.data_ptr()), dst.device.index,
+                                            ctypes.c_void_p(src.data_ptr()), src.device.index,
+                                            nbytes, ctypes.c_void_p(src_stream.cuda_stream),
+                                            ctypes.c_void_p(on.cuda_stream)))
     return dst

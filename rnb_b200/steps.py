@@ -52,6 +52,30 @@ except Exception:  # noqa: BLE001
 # because output_shape() is static and evaluated in the main process.
 MAX_CLIPS = int(os.environ.get('RNB_B200_MAX_CLIPS', '15'))
 NUM_CLASSES = 400
+# What travels between the loader and the runner.  'fp32' is the reference's wire: fp32
+# (n, 3, 8, 112, 112), 1.2 MB per clip (control.py:41, models/r2p1d/model.py:149-150).  'uint8' ships
+# the frames as the decoder produced them, uint8 (n, 8, 3, 112, 112), a quarter of the bytes, and
+# the network's first kernel does the float()/permute; it needs shared buffers that know their
+# dtype (rnb_b200.handoff.TensorEvent, installed by scripts/run_rnb.py).  Static for the same reason
+# MAX_CLIPS is: output_shape() / output_dtype() are evaluated in RnB's main process.
+WIRE = os.environ.get('RNB_B200_WIRE', 'fp32')
+if WIRE not in ('fp32', 'uint8'):
+    raise ValueError("RNB_B200_WIRE must be 'fp32' or 'uint8', got %r" % WIRE)
+
+
+def _clip_tensor_shape():
+    return (MAX_CLIPS, 8, 3, 112, 112) if WIRE == 'uint8' else (MAX_CLIPS, 3, 8, 112, 112)
+
+
+def _clip_tensor_dtype():
+    return torch.uint8 if WIRE == 'uint8' else torch.float32
+
+
+def _default_prepare_batches(max_batch):
+    """Clip counts RnB's pipelines produce: 1 or 15 clips per video (sampler.py:58-59), 3-5 after
+    3-way segmenting (control.py:66), 3 from Batcher(batch=3) (config/rnb.json:15), the nominal 10
+    of the shape tables (model.py:29-33) and the configured cap."""
+    return sorted(b for b in {1, 3, 4, 5, 10, 15, MAX_CLIPS} if b <= max_batch)
 
 
 def _resolve_state_dict(start_index, end_index, num_classes, layer_sizes, checkpoint, state_dict,
@@ -93,7 +117,7 @@ class R2P1DRunner(RunnerModel):
 
     def __init__(self, device, start_index=1, end_index=5, num_classes=NUM_CLASSES,
                  layer_sizes=None, block_type=None, dtype='bf16', checkpoint=None, state_dict=None,
-                 seed=0, max_batch=64, warmup=3):
+                 seed=0, max_batch=64, warmup=3, prepare_batches=None):
         super(R2P1DRunner, self).__init__(device)
         from .engine import R2P1DEngine
         if start_index < 1:
@@ -112,7 +136,12 @@ class R2P1DRunner(RunnerModel):
                                  state_dict, seed)
         self.model = R2P1DEngine(device, sd, start_index, end_index, num_classes, layer_sizes,
                                  dtype=dtype, max_batch=max(max_batch, MAX_CLIPS))
-        # warm up with a few inferences, as the reference does (model.py:66-71)
+        # Kernel selection for every clip count the pipeline can hand us, here rather than inside
+        # the first live request of each size (the reference pays for cudnn.benchmark there,
+        # runner.py:25), then a few warm-up inferences as the reference does (model.py:66-71).
+        if prepare_batches is None:
+            prepare_batches = _default_prepare_batches(self.model.max_batch)
+        self.model.prepare(*prepare_batches)
         stream = torch.cuda.current_stream()
         tmp = torch.randn(*self.input_shape()[0], dtype=torch.float32, device=device)
         for _ in range(warmup):
@@ -144,7 +173,8 @@ class R2P1DVideoPathIterator(VideoPathIterator):
 
 
 class R2P1DLoader(RunnerModel):
-    """Produces the fp32 (n, 3, 8, 112, 112) clip tensor of one video."""
+    """Produces the clip tensor of one video: fp32 (n, 3, 8, 112, 112) like the reference, or the
+    raw uint8 (n, 8, 3, 112, 112) frames when ``RNB_B200_WIRE=uint8``."""
 
     def __init__(self, device, num_clips_population=[1, 15], num_clips_weights=[10, 1], seed=0):
         super(R2P1DLoader, self).__init__(device)
@@ -162,6 +192,8 @@ class R2P1DLoader(RunnerModel):
     def __call__(self, tensors, non_tensors, time_card):
         frames = self.clips.next()
         time_card.num_clips = frames.shape[0]
+        if WIRE == 'uint8':
+            return (frames,), None, time_card
         # float() + permute(0, 2, 1, 3, 4) of model.py:149-150, written contiguously in one pass
         frames = self._preprocess(frames, out=self.out[:frames.shape[0]])
         return (frames,), None, time_card
@@ -171,7 +203,11 @@ class R2P1DLoader(RunnerModel):
 
     @staticmethod
     def output_shape():
-        return ((MAX_CLIPS, 3, 8, 112, 112),)
+        return (_clip_tensor_shape(),)
+
+    @staticmethod
+    def output_dtype():
+        return (_clip_tensor_dtype(),)
 
 
 class R2P1DSingleStep(RunnerModel):
@@ -189,6 +225,7 @@ class R2P1DSingleStep(RunnerModel):
         self.model = R2P1DEngine(device, sd, 1, 5, num_classes, full_sizes, dtype=dtype,
                                  max_batch=max(max_batch, MAX_CLIPS))
         self.clips = _SyntheticClips(self.device, num_clips_population, num_clips_weights, seed)
+        self.model.prepare(*sorted(set(num_clips_population)))
         stream = torch.cuda.current_stream()
         for _ in range(warmup):
             _ = self.model(self.clips.pool)
@@ -229,6 +266,7 @@ class R2P1DVideoClassifier(RunnerModel):
                                  max_batch=max(max_batch, MAX_CLIPS))
         self.clips = _SyntheticClips(self.device, num_clips_population, num_clips_weights, seed)
         self.cls_host = torch.empty((), dtype=torch.int32).pin_memory()
+        self.model.prepare(*sorted(set(num_clips_population)))
         stream = torch.cuda.current_stream()
         for _ in range(warmup):
             self.model.classify(self.clips.pool)
@@ -314,12 +352,16 @@ class Batcher(RunnerModel):
         self.stacked_time_cards = []
         self.buffer = None
         if batch > 1:
-            self.buffer = torch.empty(self.output_shape()[0], dtype=torch.float32,
+            self.buffer = torch.empty(self.output_shape()[0], dtype=_clip_tensor_dtype(),
                                       device=self.device)
 
     @staticmethod
     def output_shape():
-        return ((MAX_CLIPS, 3, 8, 112, 112),)
+        return (_clip_tensor_shape(),)
+
+    @staticmethod
+    def output_dtype():
+        return (_clip_tensor_dtype(),)
 
     def __call__(self, tensors, non_tensors, time_card):
         if self.batch <= 1:

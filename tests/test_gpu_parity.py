@@ -40,6 +40,7 @@ def engines(lib, models):
         key = (dtype, harden)
         if key not in made:
             made[key] = R2P1DEngine(DEV, models[harden].state_dict(), dtype=dtype, max_batch=16)
+            made[key].prepare(16, 3)     # timed launch plans; other sizes derive theirs from these
         return made[key]
     return get
 
@@ -136,7 +137,7 @@ def test_batch_invariance_without_splitk(lib, tmp_path):
     code = (
         "import sys, torch; sys.path.insert(0, %r)\n"
         "from rnb_b200.engine import R2P1DEngine, random_state_dict\n"
-        "eng = R2P1DEngine('cuda:0', random_state_dict(seed=5), max_batch=16)\n"
+        "eng = R2P1DEngine('cuda:0', random_state_dict(seed=5), max_batch=16).prepare(16, 5, 1)\n"
         "g = torch.Generator().manual_seed(11)\n"
         "x = torch.randint(0, 256, (16, 8, 3, 112, 112), dtype=torch.uint8, generator=g).cuda()\n"
         "y16 = eng(x).cpu().clone(); y5 = eng(x[:5]).cpu().clone(); y1 = eng(x[3:4]).cpu().clone()\n"
@@ -151,7 +152,7 @@ def test_batch_invariance_without_splitk(lib, tmp_path):
 
 
 @pytest.mark.parametrize('dtype', ['bf16', 'fp32'])
-@pytest.mark.parametrize('start,end', [(1, 1), (2, 2), (3, 3), (3, 4), (5, 5), (2, 5)])
+@pytest.mark.parametrize('start,end', [(1, 1), (2, 2), (3, 3), (4, 4), (3, 4), (5, 5), (2, 5)])
 def test_layer_ranges(lib, dtype, start, end):
     """R2P1DRunner(start_index, end_index): fp32 NCDHW in and out (models/r2p1d/model.py:29-33)."""
     from rnb_b200.engine import R2P1DEngine
@@ -162,7 +163,7 @@ def test_layer_ranges(lib, dtype, start, end):
     else:
         x = torch.randn(2, *R.LAYER_INPUT_SHAPE[start], generator=g).abs()
     want = R.forward(m, x)
-    eng = R2P1DEngine(DEV, m.state_dict(), start, end, dtype=dtype, max_batch=2)
+    eng = R2P1DEngine(DEV, m.state_dict(), start, end, dtype=dtype, max_batch=2).prepare(2)
     got = eng(x.to(DEV)).cpu()
     assert got.shape == want.shape
     if end == 5:
@@ -223,6 +224,13 @@ def test_logits_sum_argmax(lib):
     tie[:, 7] = 1.0
     tie[:, 300] = 1.0
     assert int(ops.logits_sum_argmax(tie.to(DEV))[1].item()) == 7  # numpy's lowest-index rule
+    # numpy's NaN rule: a NaN sum is the maximum, the first one wins (model.py:259 on a NaN logit)
+    nan = torch.randn(3, 400, generator=g)
+    nan[1, 250] = float('nan')
+    nan[2, 31] = float('nan')
+    assert int(ops.logits_sum_argmax(nan.to(DEV))[1].item()) == int(nan.numpy().sum(axis=0).argmax()) == 31
+    allnan = torch.full((2, 400), float('nan'))
+    assert int(ops.logits_sum_argmax(allnan.to(DEV))[1].item()) == 0
 
 
 def test_pool_fc_classify_standalone(lib):
@@ -421,7 +429,7 @@ def test_chunked_schedule_gives_identical_logits(lib, tmp_path):
         "import sys, torch; sys.path.insert(0, %r)\n"
         "from rnb_b200.engine import R2P1DEngine, random_state_dict\n"
         "sd = random_state_dict(seed=3)\n"
-        "eng = R2P1DEngine('cuda:0', sd, max_batch=16)\n"
+        "eng = R2P1DEngine('cuda:0', sd, max_batch=16).prepare(16)\n"
         "g = torch.Generator().manual_seed(9)\n"
         "x = torch.randint(0, 256, (16, 8, 3, 112, 112), dtype=torch.uint8, generator=g).cuda()\n"
         "y = eng(x).cpu(); torch.cuda.synchronize()\n"
@@ -449,7 +457,7 @@ def test_plan_cache_reproduces_the_plan(lib, tmp_path):
     code = (
         "import sys, torch; sys.path.insert(0, %r)\n"
         "from rnb_b200.engine import R2P1DEngine, random_state_dict\n"
-        "eng = R2P1DEngine('cuda:0', random_state_dict(seed=7), max_batch=16)\n"
+        "eng = R2P1DEngine('cuda:0', random_state_dict(seed=7), max_batch=16).prepare(16)\n"
         "g = torch.Generator().manual_seed(13)\n"
         "x = torch.randint(0, 256, (16, 8, 3, 112, 112), dtype=torch.uint8, generator=g).cuda()\n"
         "y = eng(x).cpu().clone(); torch.cuda.synchronize()\n"
