@@ -26,7 +26,7 @@ LAYER_SIZES = {'r18': [2, 2, 2, 2, 2], 'r34': [2, 3, 4, 6, 3]}  # runner form: s
 GFLOP_PER_CLIP = {'r18': 42.172, 'r34': 76.853}
 METRIC = 'R(2+1)D clips/sec (8x112x112 clips)'
 CLIP_BYTES = 8 * 3 * 112 * 112
-NCU_DRAM_BYTES_PER_CONV_LAUNCH = 50.5e6  # profiles/r01_ncu_launches_v3.md (1717.8 MB / 34 launches)
+NCU_LAUNCHES = os.path.join(ROOT, 'profiles', 'r02_ncu_launches.json')  # see ncu_traffic()
 FALLBACK_PEAK_TFLOPS = 1590.0  # /opt/skills/guides/B200_PROFILING.md, used only without MEASURED_PEAKS.json
 
 
@@ -40,17 +40,45 @@ def parse_args():
     ap.add_argument('--dtype', choices=['bf16', 'fp32'], default='bf16')
     ap.add_argument('--impl', choices=['b200', 'reference'], default='b200')
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--ref-clips', type=int, default=4,
-                    help='clips per step of the CPU reference arm (a bounded sample of the batch)')
+    ap.add_argument('--ref-clips', type=int, default=0,
+                    help='clips per step of the CPU arms (0: the whole batch when the run fits a few '
+                         'minutes, else a bounded sample of it)')
     ap.add_argument('--profile-table', default=None,
                     help='write the per-kernel timing table (markdown) to this path')
     return ap.parse_args()
 
 
 def base_config(args, world):
-    return {'workload': workload_name(args), 'batch': args.batch, 'clip': '3x8x112x112 uint8',
+    """The `config` object of the JSON line; both arms print the same one."""
+    B = args.batch
+    pool_n = input_pool_batches(B)
+    return {'workload': workload_name(args), 'batch': B, 'clip': '3x8x112x112 uint8',
             'weights': 'random-init (seed 0), BatchNorm folded (inference statistics)',
-            'parallelism': 'replica x%d, no collective' % world}
+            'parallelism': 'replica x%d, no collective' % world,
+            'l2': 'inputs larger than L2: %d distinct %.1f MB uint8 batches (%.0f MB) '
+                  'round-robin; per-step activation traffic also exceeds the 126 MB L2'
+                  % (pool_n, B * CLIP_BYTES / 1e6, pool_n * B * CLIP_BYTES / 1e6),
+            'e2e_path': 'rnb_b200.engine.HostPipeline: pinned uint8 frames -> H2D (copy '
+                        'stream, overlaps the previous forward) -> R2P1DEngine.forward (fused '
+                        'preprocess) -> D2H logits to pinned memory, read on the host every step'}
+
+
+def input_pool_batches(batch):
+    return max(2, -(-160 * 1024 * 1024 // (batch * CLIP_BYTES)))
+
+
+def ncu_traffic(model, dtype, batch, world):
+    """DRAM bytes (read + write) per convolution launch from the committed ncu capture of this
+    configuration (profiles/r02_ncu_launches.json, written by tools/ncu_summary.py), or None."""
+    try:
+        cap = json.load(open(NCU_LAUNCHES))
+    except Exception:  # noqa: BLE001
+        return None, None
+    key = '%s-%s-b%d' % (model, dtype, batch)
+    e = cap.get(key)
+    if not e or world != 1:
+        return None, None
+    return e.get('dram_bytes_per_conv_launch'), e.get('source')
 
 
 def workload_name(args):
@@ -132,24 +160,40 @@ def time_oracle(model_name, clips_per_step, steps, warmup, threads=None):
     return clips_per_step * steps / dt, dt / steps, torch.get_num_threads()
 
 
+def pick_cpu_sample(args, steps, budget_s):
+    """Clips per step for a CPU arm: the whole batch if `steps` of it fit `budget_s`, else the
+    largest power-of-two sample that does.  Returns (clips, seconds per step at that size)."""
+    if args.ref_clips > 0:
+        clips = min(args.ref_clips, args.batch)
+        _, per_step, _ = time_oracle(args.model, clips, 1, 1)
+        return clips, per_step
+    clips = args.batch
+    while True:
+        _, per_step, _ = time_oracle(args.model, clips, 1, 1)
+        if per_step * steps <= budget_s or clips == 1:
+            return clips, per_step
+        clips = max(1, clips // 2)
+
+
 def run_reference(args, rank):
-    """--impl reference: the CPU implementation of the path on the host cores, rank 0 only."""
+    """--impl reference: the CPU implementation of the path on the host cores, rank 0 only.
+
+    Times exactly --steps steps after --warmup warm-up steps; a step is the forward pass over the
+    same batch the GPU arm uses, or -- when that would not end within a few minutes -- over a bounded
+    sample of it (stated in `cpu_baseline.sample`; `ms_per_step` is what was timed)."""
     if rank != 0:
         return
     steps, warmup = max(1, args.steps), max(0, args.warmup)
-    # keep the whole run within a few minutes: probe one step, then cap the step count
-    probe, per_step, threads = time_oracle(args.model, args.ref_clips, 1, 1)
-    budget_s = 150.0
-    steps_run = max(1, min(steps, int(budget_s / max(per_step, 1e-3))))
-    warm_run = min(warmup, 2)
-    value, per_step, threads = time_oracle(args.model, args.ref_clips, steps_run, warm_run)
-    sample = ('%d of %d steps, %d-clip sample of the batch-%d step, oracle/r2p1d_ref.py '
-              '(torch fp32 CPU port; the reference submodule is absent)'
-              % (steps_run, steps, args.ref_clips, args.batch))
+    clips, _ = pick_cpu_sample(args, steps + warmup, 150.0)
+    value, per_step, threads = time_oracle(args.model, clips, steps, warmup)
+    sample = ('%d timed steps of %d clips each%s, oracle/r2p1d_ref.py (torch fp32 CPU port; the '
+              'reference\'s own submodule is absent)'
+              % (steps, clips, '' if clips == args.batch
+                 else ' (a sample of the batch-%d step)' % args.batch))
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': 'clips/s',
-        'n_gpus': args.gpus, 'steps': steps_run, 'warmup': warm_run,
-        'ms_per_step': per_step * 1e3 * args.batch / args.ref_clips,
+        'n_gpus': args.gpus, 'steps': steps, 'warmup': warmup,
+        'ms_per_step': per_step * 1e3, 'clips_per_step': clips,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic', 'config': base_config(args, args.gpus),
         'cpu_baseline': {'value': value, 'unit': 'clips/s', 'cores': threads, 'kind': 'port',
@@ -170,6 +214,51 @@ def peaks():
             'MEASURED_PEAKS.json bf16_tflops (burst, of measured)'
     except Exception:  # noqa: BLE001
         return FALLBACK_PEAK_TFLOPS, 1400.0, 'fallback 1.59 PFLOP/s (of fallback)'
+
+
+def run_plugin_leg(args, dev, sd, ls, K, W, rdist, barrier):
+    """clips/s through rnb_b200.steps.R2P1DLoader -> handoff -> R2P1DRunner driven the way
+    runner.py:80-173 drives them (uint8 wire, event-fenced copies, no queues or processes)."""
+    import torch
+    os.environ['RNB_B200_MAX_CLIPS'] = str(max(args.batch, 15))
+    os.environ['RNB_B200_WIRE'] = 'uint8'
+    from rnb_b200 import handoff, steps
+    from rnb_b200.timecard import TimeCard
+    B = args.batch
+    loader = steps.R2P1DLoader(dev, num_clips_population=[B], num_clips_weights=[1], seed=0)
+    runner = steps.R2P1DRunner(dev, layer_sizes=ls, state_dict=sd, dtype=args.dtype,
+                               max_batch=max(B, 16), prepare_batches=[B], warmup=1)
+    ring = [handoff.TensorEvent(steps.R2P1DLoader.output_shape(), dev,
+                                dtype=steps.R2P1DLoader.output_dtype()) for _ in range(4)]
+    placeholder = torch.zeros_like(ring[0].tensors[0])
+    host = [torch.empty((B, 400), dtype=torch.float32).pin_memory() for _ in range(2)]
+    done = [torch.cuda.Event() for _ in range(2)]
+
+    def step(i):
+        tc = TimeCard(i)
+        (frames,), _, tc = loader(None, 'synthetic/video_%07d.mp4' % i, tc)
+        te = ring[i % len(ring)]
+        n = handoff.publish(te, frames)
+        x = handoff.fetch(placeholder, te, n)
+        (logits,), _, tc = runner((x,), None, tc)
+        done[i % 2].synchronize()          # the host consumed this slot's previous result
+        host[i % 2].copy_(logits, non_blocking=True)
+        done[i % 2].record()
+
+    for i in range(W):
+        step(i)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(K):
+        step(i)
+    ev1.record()
+    barrier()
+    value, ms = rdist.whole_job_throughput(K * B, ev0.elapsed_time(ev1), dev)
+    return {'value': value, 'unit': 'clips/s', 'ms_per_step': ms / K,
+            'path': 'steps.R2P1DLoader.__call__ -> handoff.publish/fetch (uint8 TensorEvent ring, '
+                    'CUDA-event fenced) -> steps.R2P1DRunner.__call__ -> D2H logits; device-resident '
+                    'synthetic frames as in RnB, where the decoder writes GPU memory'}
 
 
 def run_b200(args, rank, world, local_rank):
@@ -194,9 +283,11 @@ def run_b200(args, rank, world, local_rank):
     ls = LAYER_SIZES[args.model]
     sd = random_state_dict(1, 5, 400, ls, seed=0)
     engine = R2P1DEngine(dev, sd, 1, 5, 400, ls, dtype=args.dtype, max_batch=max(B, 16))
+    # kernel selection ahead of the loop (the per-video latency leg below runs 1 and 15 clips)
+    engine.prepare(B, 1, 15)
 
     # inputs larger than L2: a pool of distinct uint8 batches (> 126 MB) visited round-robin
-    pool_n = max(2, -(-160 * 1024 * 1024 // (B * CLIP_BYTES)))
+    pool_n = input_pool_batches(B)
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     pool = torch.randint(0, 256, (pool_n, B, 8, 3, 112, 112), dtype=torch.uint8, device=dev,
                          generator=g)
@@ -231,17 +322,30 @@ def run_b200(args, rank, world, local_rank):
                for _ in range(4)]
     pipe = HostPipeline(engine, B)
 
+    prev = None
     for i in range(W):
-        pipe.submit(host_in[i % len(host_in)])
+        slot = pipe.submit(host_in[i % len(host_in)])
+        if prev is not None:
+            pipe.result(prev)
+        prev = slot
+    pipe.result(prev)
     barrier()
     ev0.record()
-    last = 0
+    prev, checksum = None, 0.0
     for i in range(K):
-        last = pipe.submit(host_in[i % len(host_in)])
+        slot = pipe.submit(host_in[i % len(host_in)])
+        if prev is not None:
+            # every step's logits are read on the host (one batch stays in flight meanwhile)
+            checksum += float(pipe.result(prev)[0, 0])
+        prev = slot
+    checksum += float(pipe.result(prev)[0, 0])
     ev1.record()
-    pipe.result(last)
     barrier()
     value_e2e, ms_e2e = rdist.whole_job_throughput(K * B, ev0.elapsed_time(ev1), dev)
+
+    # ---- the same through the plugin classes RnB loads from config/r2p1d-whole.json: loader step
+    #      -> shared buffer (publish / fetch) -> runner step -> logits to pinned host memory
+    plugin = run_plugin_leg(args, dev, sd, ls, K, W, rdist, barrier)
 
     # ---- per-video latency (second half of BASELINE's metric): one video = 1 or 15 clips drawn
     #      10:1 like the reference's sampler (models/r2p1d/sampler.py:58-59), host frames in, class
@@ -301,8 +405,15 @@ def run_b200(args, rank, world, local_rank):
     for e in by_kernel.values():
         e['tflops'] = e['gflop'] / e['us'] * 1e3 if e['us'] > 0 else 0.0
         e['frac'] = e['tflops'] / peak_burst
-    achieved = conv_flops / (conv_ms * 1e-3) / 1e12
+    # serialised diagnostic: the event between launches switches programmatic dependent launch off,
+    # so these per-kernel times sum to MORE than the real step
+    achieved_serial = conv_flops / (conv_ms * 1e-3) / 1e12
     n_conv = len(info)
+    # the figure that can be checked from the line itself: algorithmic FLOPs of the step over the
+    # timed step, with the kernels launched back to back exactly as in the timed region
+    step_flops = GFLOP_PER_CLIP[args.model] * 1e9 * B
+    achieved = step_flops / (ms / K * 1e-3) / 1e12
+    traffic, traffic_src = ncu_traffic(args.model, args.dtype, B, world)
 
     if args.profile_table and rank == 0:
         with open(args.profile_table, 'w') as f:
@@ -318,12 +429,12 @@ def run_b200(args, rank, world, local_rank):
     # ---- CPU baseline beside it (rank 0, N = 1 only): a bounded sample of the same workload
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        probe, per_step, threads = time_oracle(args.model, args.ref_clips, 1, 1)
+        clips, per_step = pick_cpu_sample(args, 8, 20.0)
         n = max(1, min(8, int(15.0 / max(per_step, 1e-3))))
-        v, per_step, threads = time_oracle(args.model, args.ref_clips, n, 0)
+        v, per_step, threads = time_oracle(args.model, clips, n, 0)
         cpu = {'value': v, 'unit': 'clips/s', 'cores': threads, 'kind': 'port',
                'sample': '%d steps of %d clips (of the batch-%d step), oracle/r2p1d_ref.py torch fp32'
-                         % (n, args.ref_clips, B)}
+                         % (n, clips, B)}
 
     if world > 1:
         dist.barrier()
@@ -335,35 +446,32 @@ def run_b200(args, rank, world, local_rank):
         'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': ms / K,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype,
         'data': 'synthetic',
-        'config': dict(base_config(args, world), **{
-                   'l2': 'inputs larger than L2: %d distinct %.1f MB uint8 batches (%.0f MB) '
-                         'round-robin; per-step activation traffic also exceeds the 126 MB L2'
-                         % (pool_n, B * CLIP_BYTES / 1e6, pool_n * B * CLIP_BYTES / 1e6),
-                   'e2e_path': 'rnb_b200.engine.HostPipeline: pinned uint8 frames -> H2D (copy '
-                               'stream, overlaps the previous forward) -> R2P1DEngine.forward (fused '
-                               'preprocess) -> D2H logits to pinned memory, every step'}),
+        'config': base_config(args, world),
         'e2e': {'value': value_e2e, 'unit': 'clips/s',
                 'h2d_bytes_per_step': pipe.h2d_bytes, 'd2h_bytes_per_step': pipe.d2h_bytes},
         'gpu_launches': K * engine.num_launches,
         'clocks': clocks,
         'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak_burst,
                      'unit': 'TFLOP/s', 'frac': achieved / peak_burst,
-                     # dram__bytes_read + write per convolution launch (average over the 34 launches
-                     # of one step), ncu capture in profiles/r01_ncu_launches_v3.md; only valid for
-                     # the configuration that capture was taken on
-                     'traffic': NCU_DRAM_BYTES_PER_CONV_LAUNCH
-                     if (args.model, args.dtype, B, world) == ('r18', 'bf16', 16, 1) else None,
-                     'traffic_unit': 'bytes',
+                     'how': 'whole step: %.3f GFLOP/clip x %d clips / ms_per_step (the %d convolution '
+                            'launches are %.1f%% of the step; kernels back to back with programmatic '
+                            'dependent launch, as timed)' % (GFLOP_PER_CLIP[args.model], B, n_conv,
+                                                             100 * conv_ms / (conv_ms + other_ms)),
+                     'traffic': traffic, 'traffic_unit': 'bytes per convolution launch',
+                     'traffic_source': traffic_src,
                      'algorithmic_bytes_per_launch': sum(a * B + w for _, _, a, w, _ in info) / n_conv,
                      'kernel': 'tcgen05 implicit-GEMM convolutions: conv_tc_kernel + conv_pair_kernel + conv_splitk_kernel + '
                                'conv_patch_kernel (%d launches per step)' % n_conv,
-                     'by_kernel': by_kernel,
                      'peak_source': peak_src, 'frac_of_sustained': achieved / peak_sust,
                      'flops_per_launch_avg': conv_flops / n_conv,
-                     'us_per_launch_avg': conv_ms * 1e3 / n_conv,
+                     'us_per_launch_avg': ms / K * 1e3 * conv_ms / (conv_ms + other_ms) / n_conv,
                      'kernel_share_of_step': conv_ms / (conv_ms + other_ms),
-                     'whole_step_frac': (GFLOP_PER_CLIP[args.model] * 1e9 * B) /
-                                        (ms / K * 1e-3) / 1e12 / peak_burst},
+                     'serialised': {'note': 'CUDA event between launches = programmatic dependent '
+                                            'launch OFF; sums exceed the real step; diagnostic only',
+                                    'achieved': achieved_serial, 'frac': achieved_serial / peak_burst,
+                                    'conv_us_sum': conv_ms * 1e3, 'other_us_sum': other_ms * 1e3,
+                                    'by_kernel': by_kernel}},
+        'e2e_plugin': plugin,
         'cpu_baseline': cpu,
         'latency': lat,
     }
