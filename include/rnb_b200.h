@@ -93,6 +93,12 @@ int rnb_r2p1d_prepare(void* handle, int batch, void* stream);
 int rnb_r2p1d_force_kernel(void* handle, int batch, int op, int kind, int cm, int cn, int ks,
                            int block_n, int pair);
 
+/* The other half of the hook (no counterpart in the reference): what the plan of `batch` clips
+ * currently runs convolution `op` with -- out7 = {kind, cm, cn, ks, block_n, pair, tuned}, the
+ * arguments rnb_r2p1d_force_kernel takes plus 1 if the plan was timed by rnb_r2p1d_prepare.
+ * RNB_ESTATE while the handle has no plan for that batch size. */
+int rnb_r2p1d_plan_entry(void* handle, int batch, int op, int out7[7]);
+
 /* One forward pass over `batch` clips.  `in`/`out` are device pointers.
  *   in_fmt : U8_NTCHW (only when start_idx == 1; fuses the loader's float()+permute of
  *            models/r2p1d/model.py:149-150), F32_NCDHW (shape of model.py:29-33) or BF16_NDHWC.

@@ -35,6 +35,7 @@ PROTOTYPES = {
                                          ctypes.c_void_p]),
     'rnb_r2p1d_prepare': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),
     'rnb_r2p1d_force_kernel': (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 8),
+    'rnb_r2p1d_plan_entry': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, _c_int_p]),
     'rnb_r2p1d_classify': (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                           ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                           ctypes.c_void_p, ctypes.c_void_p]),

@@ -129,6 +129,14 @@ int rnb_r2p1d_force_kernel(void* handle, int batch, int op, int kind, int cm, in
   return RNB_OK;
 }
 
+int rnb_r2p1d_plan_entry(void* handle, int batch, int op, int out7[7]) {
+  auto* m = static_cast<rnb::R2P1DModel*>(handle);
+  if (!m || !out7) return fail(RNB_EINVAL, "bad argument to rnb_r2p1d_plan_entry");
+  if (!m->plan_entry(batch, op, out7))
+    return fail(RNB_ESTATE, "no launch plan for this batch size and convolution yet");
+  return RNB_OK;
+}
+
 int rnb_r2p1d_classify(void* handle, const void* in, int in_fmt, int batch, float* logits,
                        float* sum, int* cls, void* stream) {
   if (!handle) return fail(RNB_EINVAL, "handle is NULL");

@@ -72,10 +72,23 @@ inline int conv_patch_smem_bytes(int nkb, int patch_rows, int num_taps, int bloc
   const int wbytes = b_stages > 0 ? b_stages * block_n * 128
                                   : num_taps * block_n * (nkb * 128 + tail_ch * 2);
   // (res_blocks: 64-channel blocks of a residual tile, two tiles in flight)
-  return 1024 + wbytes + p_bufs * patch_rows * (nkb * 128 + tail_ch * 2) + 1024 /*slack rows*/ +
-         2 * res_blocks * 16384 + 256 + kMaxBlockN * 4;
+  // 1024 alignment slack, 2048 control block (barrier areas, shift table, TMEM address)
+  return 1024 + 2048 + wbytes + p_bufs * patch_rows * (nkb * 128 + tail_ch * 2) +
+         1024 /*slack rows*/ + 2 * res_blocks * 16384;
 }
 
 cudaError_t launch_conv_patch(const ConvPatchParams& p, int num_sms, cudaStream_t stream);
+
+// Co-scheduled SpatioTemporalConv (conv_patch.cu): `sp` = the 1 x k x k convolution, `tp` = the
+// k x 1 x 1 convolution reading sp's output, both resident-weight single-CTA patch plans over the
+// same batch.  n_sp of the grid's CTAs start on the spatial convolution, the others on the
+// temporal one; temporal items are claimed `chunk` at a time from a grid-wide counter, so the
+// spatial CTAs take their share of what is left when they are done.
+// `flags`: device array of (flag_clips + 2) zero-initialised 64-bit counters, flag_clips >= batch,
+// owned by the caller and shared by all such launches of a stream (each launch re-zeroes it).
+bool conv_patch_dual_applicable(const ConvPatchParams& sp, const ConvPatchParams& tp);
+cudaError_t launch_conv_patch_dual(const ConvPatchParams& sp, const ConvPatchParams& tp, int n_sp,
+                                   int chunk, unsigned long long* flags, int flag_clips,
+                                   int num_sms, cudaStream_t stream);
 
 }  // namespace rnb

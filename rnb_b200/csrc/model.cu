@@ -886,6 +886,23 @@ const std::vector<R2P1DModel::Launch>* R2P1DModel::ensure_plan(int batch, cudaSt
   return &plans_[batch];
 }
 
+bool R2P1DModel::plan_entry(int batch, int op, int out[7]) const {
+  const auto it = plans_.find(batch);
+  if (it == plans_.end()) return false;
+  for (const Launch& l : it->second)
+    if (l.op == op) {
+      out[0] = l.patch ? 2 : (l.tc.pair ? (l.tc.tpatch ? 5 : 4) : (l.tc.ks > 1 ? 3 : 1));
+      out[1] = l.patch ? 1 : l.tc.cm;
+      out[2] = l.patch ? 1 : l.tc.cn;
+      out[3] = l.patch ? 0 : l.tc.ks;
+      out[4] = l.patch ? l.pp.block_n : l.tc.block_n;
+      out[5] = l.patch ? l.pp.pair : l.tc.pair;
+      out[6] = tuned_.count(batch) ? 1 : 0;
+      return true;
+    }
+  return false;
+}
+
 int R2P1DModel::prepare(int batch, cudaStream_t stream, std::string* err) {
   if (!finalized_) {
     if (err) *err = "prepare before finalize";

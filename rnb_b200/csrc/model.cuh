@@ -61,6 +61,8 @@ class R2P1DModel {
   int force_kernel(int batch, int op, int kind, int cm, int cn, int ks, int block_n, int pair,
                    std::string* err);
   bool plan_is_tuned(int batch) const { return tuned_.count(batch) != 0; }
+  // The plan entry of convolution `op` at `batch`: {kind, cm, cn, ks, block_n, pair, tuned}.
+  bool plan_entry(int batch, int op, int out[7]) const;
   bool op_info(int op, std::string* name, double* flops_per_clip, double* act_bytes_per_clip,
                double* weight_bytes, int* kernel_kind) const;
   void io_shape(int which, int64_t shape4[4]) const;

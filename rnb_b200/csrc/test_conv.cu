@@ -576,8 +576,143 @@ static bool run_stem(int B) {
   return pass;
 }
 
+// Co-scheduled SpatioTemporalConv (conv_patch_dual_kernel): the 1x3x3 and the 3x1x1 convolution of
+// one conv2-stage module in ONE launch must give bit-identical output to the two launches (same
+// kernels, same K order), for several CTA splits and tail sizes, launched back to back so that a
+// counter left dirty by one launch would break the next.
+static bool run_dual(int B, bool residual, int perf_iters) {
+  const ConvGeom gs = geom(8, 56, 56, 64, 144, 1, 3, 3, 1, 1, 1, 0, 1, 1);
+  const ConvGeom gt = geom(8, 56, 56, 144, 64, 3, 1, 1, 1, 1, 1, 1, 0, 0);
+  const size_t pos = (size_t)B * 8 * 56 * 56;
+  std::vector<uint16_t> xb(pos * 64), rb(pos * 64);
+  for (auto& v : xb) v = f32_to_bf16_bits(frand());
+  for (auto& v : rb) v = f32_to_bf16_bits(frand());
+  auto make_w = [](const ConvGeom& g, std::vector<uint16_t>* wp, std::vector<float>* shift) {
+    std::vector<float> w((size_t)g.cout * g.cin * g.kt * g.kh * g.kw), scale(g.cout_pad(), 0.f);
+    const float amp = 1.7f / sqrtf((float)(g.cin * g.kt * g.kh * g.kw));
+    for (auto& v : w) v = bf16_round(frand() * amp);
+    shift->assign(g.cout_pad(), 0.f);
+    for (int n = 0; n < g.cout; ++n) {
+      scale[n] = 0.75f + 0.5f * fabsf(frand());
+      (*shift)[n] = 0.2f * frand();
+    }
+    pack_conv_weights_tc(g, w.data(), scale.data(), wp);
+  };
+  std::vector<uint16_t> ws, wt;
+  std::vector<float> shs, sht;
+  make_w(gs, &ws, &shs);
+  make_w(gt, &wt, &sht);
+  __nv_bfloat16 *dx, *dr, *dws, *dwt, *dmid, *dy1, *dy2;
+  float *dshs, *dsht;
+  unsigned long long* dflags;
+  const int flag_clips = 64;
+  CK(cudaMalloc(&dx, xb.size() * 2));
+  CK(cudaMalloc(&dr, rb.size() * 2));
+  CK(cudaMalloc(&dws, ws.size() * 2));
+  CK(cudaMalloc(&dwt, wt.size() * 2));
+  CK(cudaMalloc(&dmid, pos * 144 * 2));
+  CK(cudaMalloc(&dy1, pos * 64 * 2));
+  CK(cudaMalloc(&dy2, pos * 64 * 2));
+  CK(cudaMalloc(&dshs, shs.size() * 4));
+  CK(cudaMalloc(&dsht, sht.size() * 4));
+  CK(cudaMalloc(&dflags, (flag_clips + 2) * 8));
+  CK(cudaMemset(dflags, 0, (flag_clips + 2) * 8));
+  CK(cudaMemcpy(dx, xb.data(), xb.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dr, rb.data(), rb.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dws, ws.data(), ws.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dwt, wt.data(), wt.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dshs, shs.data(), shs.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dsht, sht.data(), sht.size() * 4, cudaMemcpyHostToDevice));
+  ConvPatchParams ps, pt1, pt2;
+  std::string err;
+  if (!build_conv_patch_params(gs, B, dx, dws, dmid, dshs, nullptr, true, &ps, &err) ||
+      !build_conv_patch_params(gt, B, dmid, dwt, dy1, dsht, residual ? dr : nullptr, true, &pt1, &err) ||
+      !build_conv_patch_params(gt, B, dmid, dwt, dy2, dsht, residual ? dr : nullptr, true, &pt2, &err)) {
+    printf("dual: PLAN FAILED: %s\n", err.c_str());
+    return false;
+  }
+  if (!conv_patch_dual_applicable(ps, pt2)) {
+    printf("dual: not applicable\n");
+    return false;
+  }
+  CK(launch_conv_patch(ps, num_sms, 0));
+  CK(launch_conv_patch(pt1, num_sms, 0));
+  CK(cudaDeviceSynchronize());
+  std::vector<uint16_t> y1(pos * 64), y2(pos * 64);
+  CK(cudaMemcpy(y1.data(), dy1, y1.size() * 2, cudaMemcpyDeviceToHost));
+  bool pass = true;
+  // {CTAs that start on the spatial convolution, temporal items per claim}
+  const int splits[][2] = {{num_sms * 3 / 4, 4}, {num_sms * 3 / 4, 1}, {num_sms - 8, 2}, {num_sms / 2, 4},
+                           {num_sms * 4 / 5, 8}, {1, 3}};
+  for (const auto& sp : splits) {
+    CK(cudaMemset(dmid, 0xff, pos * 144 * 2));
+    CK(cudaMemset(dy2, 0xff, pos * 64 * 2));
+    for (int rep = 0; rep < 2; ++rep)
+      CK(launch_conv_patch_dual(ps, pt2, sp[0], sp[1], dflags, flag_clips, num_sms, 0));
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+      printf("dual n_sp=%d tail=%d: %s\n", sp[0], sp[1], cudaGetErrorString(e));
+      return false;
+    }
+    CK(cudaMemcpy(y2.data(), dy2, y2.size() * 2, cudaMemcpyDeviceToHost));
+    size_t diff = 0;
+    for (size_t i = 0; i < y1.size(); ++i) diff += y1[i] != y2[i];
+    unsigned long long fl[66];
+    CK(cudaMemcpy(fl, dflags, sizeof fl, cudaMemcpyDeviceToHost));
+    bool clean = true;
+    for (int i = 0; i <= flag_clips + 1; ++i) clean = clean && fl[i] == 0;
+    printf("dual conv2 B=%d res=%d n_sp=%d chunk=%d: %zu of %zu values differ, counters %s  %s\n",
+           B, (int)residual, sp[0], sp[1], diff, y1.size(), clean ? "re-armed" : "DIRTY",
+           diff == 0 && clean ? "PASS" : "FAIL");
+    pass = pass && diff == 0 && clean;
+  }
+  if (perf_iters > 0 && pass) {
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    float ms;
+    for (int i = 0; i < 3; ++i) {
+      CK(launch_conv_patch(ps, num_sms, 0));
+      CK(launch_conv_patch(pt1, num_sms, 0));
+    }
+    CK(cudaEventRecord(e0));
+    for (int i = 0; i < perf_iters; ++i) {
+      CK(launch_conv_patch(ps, num_sms, 0));
+      CK(launch_conv_patch(pt1, num_sms, 0));
+    }
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    printf("    two launches: %.1f us per SpatioTemporalConv\n", ms * 1e3 / perf_iters);
+    for (int n_sp = num_sms / 2; n_sp <= num_sms - 6; n_sp += 8)
+      for (int tail : {2, 4, 8}) {
+        for (int i = 0; i < 2; ++i)
+          CK(launch_conv_patch_dual(ps, pt2, n_sp, tail, dflags, flag_clips, num_sms, 0));
+        CK(cudaEventRecord(e0));
+        for (int i = 0; i < perf_iters; ++i)
+          CK(launch_conv_patch_dual(ps, pt2, n_sp, tail, dflags, flag_clips, num_sms, 0));
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        printf("    dual n_sp=%3d chunk=%d: %.1f us\n", n_sp, tail, ms * 1e3 / perf_iters);
+      }
+  }
+  cudaFree(dx); cudaFree(dr); cudaFree(dws); cudaFree(dwt); cudaFree(dmid); cudaFree(dy1);
+  cudaFree(dy2); cudaFree(dshs); cudaFree(dsht); cudaFree(dflags);
+  return pass;
+}
+
 int main(int argc, char** argv) {
   const int perf_batch = argc > 1 ? atoi(argv[1]) : 0;
+  if (argc > 2 && std::string(argv[2]) == "dual") {
+    // ./test_conv 16 dual : only the co-scheduled kernel, with its split sweep
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, 0));
+    num_sms = prop.multiProcessorCount;
+    const bool ok = run_dual(perf_batch, false, 20) && run_dual(perf_batch, true, 20);
+    printf("%s\n", ok ? "ALL TESTS PASSED" : "SOME TESTS FAILED");
+    return ok ? 0 : 1;
+  }
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, 0));
   num_sms = prop.multiProcessorCount;
@@ -605,6 +740,8 @@ int main(int argc, char** argv) {
   int failed = 0;
   for (const Case& c : cases) failed += run_case(c, 0) ? 0 : 1;
   failed += run_stem(2) ? 0 : 1;
+  failed += run_dual(3, false, 0) ? 0 : 1;
+  failed += run_dual(2, true, 0) ? 0 : 1;
 
   if (perf_batch > 0 && failed == 0) {
     printf("---- perf at B=%d\n", perf_batch);

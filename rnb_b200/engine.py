@@ -205,6 +205,13 @@ class R2P1DEngine:
         _lib.check(self.lib.rnb_r2p1d_force_kernel(self._handle, int(batch), int(op), k, cm, cn, ks,
                                                    block_n, pair))
 
+    def plan_entry(self, batch, op):
+        """(kind, dict of force_kernel arguments, tuned?) of convolution ``op`` at ``batch`` clips."""
+        out = (ctypes.c_int * 7)()
+        _lib.check(self.lib.rnb_r2p1d_plan_entry(self._handle, int(batch), int(op), out))
+        return (self.KERNEL_KINDS[out[0]],
+                dict(cm=out[1], cn=out[2], ks=out[3], block_n=out[4], pair=out[5]), bool(out[6]))
+
     def op_info(self):
         """[(state_dict prefix, FLOPs per clip, activation bytes per clip, weight bytes, kernel)]
         per convolution; kernel is one of ``KERNEL_KINDS`` (what the launch plan of the most recent
