@@ -15,6 +15,8 @@ whole integration.  Three things are arranged around the unmodified driver, none
     compute process, because benchmark.py:105 treats `used == 0` as "free" and current drivers
     never report zero.
   * CUDA_VISIBLE_DEVICES (benchmark.py:94) defaults to all GPUs.
+  * --runtime b200: `runner` resolves to rnb_b200.runtime (the same worker protocol with the
+    event-fenced hand-off) instead of the reference's runner.py.
   * --wire uint8: shared tensors are built by rnb_b200.handoff.TensorEvent with the dtype the
     producing step declares (`output_dtype()`), instead of control.py:41's fixed fp32, so the loader
     ships raw uint8 frames (a quarter of the bytes); control.TensorEvent / control.load_class are
@@ -92,6 +94,9 @@ def main():
     ap = argparse.ArgumentParser(add_help=False)
     ap.add_argument('--reference', default=None)
     ap.add_argument('--wire', choices=['fp32', 'uint8'], default='fp32')
+    ap.add_argument('--runtime', choices=['reference', 'b200'], default='reference',
+                    help="worker loop: the reference's runner.py, or rnb_b200.runtime (same protocol, "
+                         'event-fenced hand-off instead of copy_ + host synchronisation)')
     ap.add_argument('--max-clips', type=int, default=15)
     ap.add_argument('--logdir', default=os.path.join(ROOT, 'gpurun_out', 'rnb'))
     ap.add_argument('--plan-cache', default=None)
@@ -117,8 +122,12 @@ def main():
     rest = [os.path.abspath(a) if a.endswith('.json') and os.path.exists(a) else a for a in rest]
     os.makedirs(args.logdir, exist_ok=True)
     os.chdir(args.logdir)
-    if args.wire != 'fp32':
+    if args.wire != 'fp32' or args.runtime == 'b200':
         install_dtype_aware_buffers()
+    if args.runtime == 'b200':
+        # benchmark.py does `from runner import runner` (benchmark.py:148): hand it our loop
+        import rnb_b200.runtime
+        sys.modules['runner'] = rnb_b200.runtime
     sys.argv = [os.path.join(ref, 'benchmark.py')] + rest
     runpy.run_path(sys.argv[0], run_name='__main__')
 

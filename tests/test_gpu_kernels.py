@@ -199,3 +199,29 @@ def test_standalone_kernel_harness(lib):
                           timeout=600)
     tail = '\n'.join(proc.stdout.splitlines()[-15:])
     assert proc.returncode == 0 and 'ALL TESTS PASSED' in proc.stdout, tail
+
+
+def test_cupti_kernel_timeline(lib):
+    """initialize / flush / report of the CUPTI bridge (reference utils/cupti.cpp:142-166, driven
+    like test_cupti.py:14-21): one record per kernel of a forward pass, with this library's kernel
+    names and start < end."""
+    from rnb_b200 import cupti
+    from rnb_b200.engine import R2P1DEngine, random_state_dict
+    eng = R2P1DEngine(DEV, random_state_dict(seed=2), max_batch=4)
+    x = torch.randint(0, 256, (4, 8, 3, 112, 112), dtype=torch.uint8, device=DEV)
+    eng(x)
+    torch.cuda.synchronize()
+    cupti.initialize()
+    cupti.report()                      # drop anything collected so far
+    eng(x)
+    torch.cuda.synchronize()
+    cupti.flush()
+    recs = cupti.report(details=True)
+    cupti.finalize()
+    ours = [r for r in recs if 'rnb::' in r[0]]
+    assert len(ours) == eng.num_launches, [r[0][:60] for r in recs]
+    assert all(r[1] < r[2] for r in ours)
+    assert any('conv_patch_kernel' in r[0] for r in ours) and any('pool_fc' in r[0] for r in ours)
+    assert [r[1] for r in ours] == sorted(r[1] for r in ours)      # one stream: launch order
+    assert cupti.report() == []                                    # report() empties the list
+    eng.close()

@@ -54,6 +54,17 @@ def test_whole_pipeline_under_the_reference_harness(lib, tmp_path, wire):
     assert 'Finished processing 60 videos' in log
 
 
+def test_whole_pipeline_with_the_event_fenced_worker_loop(lib, tmp_path):
+    """Same run with rnb_b200.runtime.runner in place of the reference's runner.py: uint8 wire,
+    ready / free CUDA events instead of copy_ + stream.synchronize(); client, queues, control plane
+    and logs still the reference's."""
+    if _reference() is None:
+        pytest.skip('no RnB checkout (RNB_REFERENCE or baseline/_ref/rnb)')
+    out, log = _run(tmp_path, 'r2p1d-whole.json', 60, extra=('--wire', 'uint8', '--runtime', 'b200'))
+    assert out['videos_logged'] >= 60 and out['termination_flag'] == 0
+    assert 'Finished processing 60 videos' in log
+
+
 def test_single_step_pipeline_under_the_reference_harness(lib, tmp_path):
     """config/r2p1d-nopipeline.json on one GPU: R2P1DSingleStep as the only (and final) step."""
     if _reference() is None:

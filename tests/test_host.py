@@ -22,11 +22,22 @@ def test_library_exports_every_declared_symbol(lib):
         assert hasattr(lib, name), name
 
 
-def test_every_entry_point_cites_the_reference():
-    header = open(os.path.join(ROOT, 'include', 'rnb_b200.h')).read()
+def test_cupti_library_exports_every_declared_symbol():
+    from rnb_b200 import cupti
+    header = open(os.path.join(ROOT, 'include', 'rnb_cupti.h')).read()
+    declared = set(re.findall(r'\b(rnb_cupti_[a-z0-9_]+)\s*\(', header))
+    assert declared == set(cupti.PROTOTYPES), declared ^ set(cupti.PROTOTYPES)
+    lib = cupti.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+
+
+@pytest.mark.parametrize('name', ['rnb_b200.h', 'rnb_cupti.h'])
+def test_every_entry_point_cites_the_reference(name):
+    header = open(os.path.join(ROOT, 'include', name)).read()
     for block in re.findall(r'/\*(?:[^*]|\*(?!/))*\*/\s*(?:int|double|void|const char\*) rnb_\w+', header):
         name = re.search(r'rnb_\w+$', block).group(0)
-        assert re.search(r'\w+\.py:\d+', block) or 'no counterpart in the reference' in block.lower(), \
+        assert re.search(r'\w+\.(py|cpp):\d+', block) or 'no counterpart in the reference' in block.lower(), \
             '%s lacks a reference citation' % name
 
 
