@@ -72,9 +72,15 @@ class TensorEvent:
         self.ready = self.free = None
         if device.type == 'cuda':
             with torch.cuda.device(device):
-                # (a wait on a never-recorded event returns at once, which is what the first use needs)
                 self.ready = torch.cuda.Event(enable_timing=False, interprocess=True)
                 self.free = torch.cuda.Event(enable_timing=False, interprocess=True)
+                # torch creates the CUDA event lazily, on whatever device is current at its first
+                # use -- which would be the pickling in the main process, on device 0.  Record both
+                # once here, on THIS device's (idle) stream: the events then belong to the buffer's
+                # device, and a first wait on either returns at once.
+                s = torch.cuda.current_stream(device)
+                self.ready.record(s)
+                self.free.record(s)
 
 
 _copy_streams = {}

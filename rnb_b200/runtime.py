@@ -40,6 +40,15 @@ def runner(input_queue, output_queues, queue_selector_path, print_summary,
     from utils.class_utils import load_class
     from rnb_b200 import handoff
 
+    # RNB_B200_RUNTIME_WATCHDOG=<seconds>: dump every thread's Python stack to stderr if the worker
+    # is still alive after that long (an exception in one RnB process leaves the others waiting at
+    # the final barrier, benchmark.py:195-197; this shows who waits where)
+    import os
+    if os.environ.get('RNB_B200_RUNTIME_WATCHDOG'):
+        import faulthandler
+        faulthandler.enable()
+        faulthandler.dump_traceback_later(float(os.environ['RNB_B200_RUNTIME_WATCHDOG']), exit=False)
+
     on_gpu = g_idx >= 0
     if on_gpu:
         torch.cuda.set_device(g_idx)
