@@ -13,7 +13,8 @@ whole integration.  Three things are arranged around the unmodified driver, none
   * `py3nvml` (benchmark.py:44) is not installed here; a stand-in module backed by `pynvml` is
     registered under that name.  Its memory query reports 0 bytes used for a GPU that runs no
     compute process, because benchmark.py:105 treats `used == 0` as "free" and current drivers
-    never report zero.
+    never report zero (RNB_B200_ALLOW_BUSY_GPUS=1 reports every GPU as free, for runs started from
+    a process that itself holds a CUDA context, such as the test suite).
   * CUDA_VISIBLE_DEVICES (benchmark.py:94) defaults to all GPUs.
   * --runtime b200: `runner` resolves to rnb_b200.runtime (the same worker protocol with the
     event-fenced hand-off) instead of the reference's runner.py.
@@ -50,10 +51,12 @@ def install_py3nvml_shim():
         def __init__(self, used, total, free):
             self.used, self.total, self.free = used, total, free
 
+    allow_busy = os.environ.get('RNB_B200_ALLOW_BUSY_GPUS') == '1'
+
     def mem_info(handle):
         m = pynvml.nvmlDeviceGetMemoryInfo(handle)
         try:
-            busy = len(pynvml.nvmlDeviceGetComputeRunningProcesses(handle)) > 0
+            busy = not allow_busy and len(pynvml.nvmlDeviceGetComputeRunningProcesses(handle)) > 0
         except Exception:  # noqa: BLE001
             busy = False
         return _Mem(m.used if busy else 0, m.total, m.free)

@@ -31,6 +31,7 @@ def _run(tmp_path, config, videos, extra=(), timeout=900):
            *extra, '-c', os.path.join(ROOT, 'config', config), '-v', str(videos), '-mi', '0']
     env = dict(os.environ)
     env.setdefault('CUDA_VISIBLE_DEVICES', '0')
+    env['RNB_B200_ALLOW_BUSY_GPUS'] = '1'   # this pytest process holds a context on the GPU
     proc = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
                           timeout=timeout, env=env)
     assert proc.returncode == 0, proc.stdout[-3000:]
@@ -78,6 +79,7 @@ def test_single_step_pipeline_under_the_reference_harness(lib, tmp_path):
            '-c', str(path), '-v', '40', '-mi', '0']
     env = dict(os.environ)
     env.setdefault('CUDA_VISIBLE_DEVICES', '0')
+    env['RNB_B200_ALLOW_BUSY_GPUS'] = '1'   # this pytest process holds a context on the GPU
     proc = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
                           timeout=900, env=env)
     assert proc.returncode == 0, proc.stdout[-3000:]

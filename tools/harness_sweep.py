@@ -66,7 +66,8 @@ def run(kind, n, videos, mi, wire, max_clips=15, timeout=1200, runtime='referenc
     tmp = tempfile.mkdtemp(prefix='rnb_%s_%d_' % (kind, n))
     path = os.path.join(tmp, '%s-%dgpu.json' % (kind, n))
     json.dump(cfg, open(path, 'w'))
-    env = dict(os.environ, CUDA_VISIBLE_DEVICES=','.join(str(i) for i in range(max(n, 1))))
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES=','.join(str(i) for i in range(max(n, 1))),
+               RNB_B200_ALLOW_BUSY_GPUS='1')
     cmd = [sys.executable, os.path.join(ROOT, 'scripts', 'run_rnb.py'), '--logdir', tmp, '--wire', wire,
            '--runtime', runtime, '--max-clips', str(max_clips), '-c', path, '-v', str(videos), '-mi', str(mi)]
     t0 = time.time()
