@@ -79,6 +79,8 @@ void R2P1DModel::release() {
   }
   if (d_classify_scratch_) cudaFree(d_classify_scratch_);
   d_classify_scratch_ = nullptr;
+  if (d_dual_flags_) cudaFree(d_dual_flags_);
+  d_dual_flags_ = nullptr;
   if (d_fc_w_) cudaFree(d_fc_w_);
   if (d_fc_b_) cudaFree(d_fc_b_);
   d_fc_w_ = d_fc_b_ = nullptr;
@@ -370,6 +372,14 @@ int R2P1DModel::finalize(std::string* err) {
       return RNB_ECUDA;
     }
   }
+  if (dtype_ == RNB_DTYPE_BF16) {
+    const size_t fb = (size_t)(max_batch_ + 2) * sizeof(unsigned long long);
+    if (!cuda_ok(cudaMalloc(&d_dual_flags_, fb), "cudaMalloc(counters)", err) ||
+        !cuda_ok(cudaMemset(d_dual_flags_, 0, fb), "cudaMemset(counters)", err)) {
+      release();
+      return RNB_ECUDA;
+    }
+  }
   params_.clear();
   finalized_ = true;
   l2_persist_acquire();
@@ -418,6 +428,7 @@ bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
       for (const Launch& l : it->second)
         if (l.op == op) {
           kind = l.patch ? 2 : (l.tc.pair ? (l.tc.tpatch ? 5 : 4) : (l.tc.ks > 1 ? 3 : 1));
+          if (l.dual_n_sp > 0 || l.merged) kind = 6;
           break;
         }
     *kernel_kind = kind;
@@ -444,7 +455,8 @@ int R2P1DModel::profile(const void* in, int in_fmt, int batch, void* out, int ou
     const std::vector<Launch>* plan = ensure_plan(batch, stream, err, false);
     last_batch_ = batch;
     if (!plan) return RNB_ECUDA;
-    for (const Launch& l : *plan) launch_op.push_back(l.op);
+    for (const Launch& l : *plan)
+      if (!l.merged) launch_op.push_back(l.op);
   } else {
     for (int i = 0; i < n_ops; ++i) launch_op.push_back(i);
   }
@@ -711,6 +723,84 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
   return true;
 }
 
+// Entry i of a plan as one launch (nothing for an entry merged into its predecessor).
+cudaError_t R2P1DModel::launch_one(const std::vector<Launch>& plan, size_t i,
+                                   cudaStream_t stream) const {
+  const Launch& l = plan[i];
+  if (l.merged) return cudaSuccess;
+  if (l.dual_n_sp > 0 && i + 1 < plan.size())
+    return launch_conv_patch_dual(l.pp, plan[i + 1].pp, l.dual_n_sp, l.dual_chunk, d_dual_flags_,
+                                  max_batch_, num_sms_, stream);
+  return l.patch ? launch_conv_patch(l.pp, num_sms_, stream) : launch_tc(l.tc, stream);
+}
+
+// Entries i, i+1 = the two convolutions of one SpatioTemporalConv, both on the resident-weight
+// patch kernel over the whole batch: the pair the co-scheduled kernel can run in one launch.
+bool R2P1DModel::dual_candidate(const std::vector<Launch>& plan, int i) const {
+  if (i + 1 >= (int)plan.size()) return false;
+  const Launch& a = plan[i];
+  const Launch& b = plan[i + 1];
+  if (!a.patch || !b.patch || a.op + 1 != b.op) return false;
+  if (ops_[a.op].out_slot != SLOT_M || ops_[b.op].in_slot != SLOT_M) return false;
+  if (a.first != 0 || b.first != 0 || a.batch != b.batch) return false;
+  return conv_patch_dual_applicable(a.pp, b.pp);
+}
+
+// Times the pair as two launches and as one co-scheduled launch at a few CTA splits; keeps the
+// co-scheduled form when it is clearly faster (it reads the intermediate tensor from L2, but the
+// two convolutions then share the SMs' bandwidth and power: it pays where BOTH are bandwidth-bound,
+// as in the stem, not where the spatial one is tensor-bound, as in conv2;
+// profiles/r02_coscheduled_conv2.md).  RNB_B200_DUAL=0 keeps it out.
+bool R2P1DModel::tune_dual(std::vector<Launch>* plan, int i, cudaStream_t stream) {
+  static const bool allow = [] {
+    const char* e = getenv("RNB_B200_DUAL");
+    return !(e && e[0] == '0');
+  }();
+  if (!allow || !dual_candidate(*plan, i)) return false;
+  Launch& a = (*plan)[i];
+  Launch& b = (*plan)[i + 1];
+  cudaEvent_t e0, e1;
+  if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) return false;
+  auto time_it = [&](auto&& launch, float* ms) -> bool {
+    cudaError_t te = launch();
+    if (te == cudaSuccess) te = cudaEventRecord(e0, stream);
+    for (int r = 0; r < 8 && te == cudaSuccess; ++r) te = launch();
+    if (te == cudaSuccess) te = cudaEventRecord(e1, stream);
+    if (te == cudaSuccess) te = cudaEventSynchronize(e1);
+    if (te == cudaSuccess) te = cudaEventElapsedTime(ms, e0, e1);
+    if (te != cudaSuccess) (void)cudaGetLastError();
+    return te == cudaSuccess;
+  };
+  float base = 0.f;
+  bool ok = time_it([&] {
+    cudaError_t e = launch_conv_patch(a.pp, num_sms_, stream);
+    return e == cudaSuccess ? launch_conv_patch(b.pp, num_sms_, stream) : e;
+  }, &base);
+  float best = base;
+  int best_n = 0;
+  static const int kPct[] = {50, 58, 66, 74, 82};
+  for (int pct : kPct) {
+    if (!ok) break;
+    const int n_sp = num_sms_ * pct / 100;
+    if (n_sp < 1 || n_sp >= num_sms_) continue;
+    float ms = 0.f;
+    ok = time_it([&] {
+      return launch_conv_patch_dual(a.pp, b.pp, n_sp, 4, d_dual_flags_, max_batch_, num_sms_, stream);
+    }, &ms);
+    if (ok && ms < best * 0.97f) {
+      best = ms;
+      best_n = n_sp;
+    }
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (!ok || best_n == 0) return false;
+  a.dual_n_sp = best_n;
+  a.dual_chunk = 4;
+  b.merged = true;
+  return true;
+}
+
 cudaError_t R2P1DModel::launch_tc(const ConvTcParams& tc, cudaStream_t stream) const {
   if (tc.pair) return launch_conv_pair(tc, num_sms_, stream);
   return tc.ks > 1 ? launch_conv_splitk(tc, num_sms_, stream) : launch_conv_tc(tc, num_sms_, stream);
@@ -760,6 +850,9 @@ bool R2P1DModel::build_plan(int batch, cudaStream_t stream, std::vector<Launch>*
     }
     ++i;  // the temporal half is planned
   }
+  if (plan->size() == ops_.size())
+    for (int i = 0; i + 1 < n; ++i)
+      if (tune_dual(plan, i, stream)) ++i;
   return true;
 }
 
@@ -801,10 +894,10 @@ bool R2P1DModel::load_cached_plan(const char* path, int batch, cudaStream_t stre
     if (sscanf(line, "plan %llx %d", &key, &n) != 2 || key != want || n != (int)ops_.size()) continue;
     found = true;
     for (int i = 0; i < n && found; ++i) {
-      int op = -1, patch = 0, cm = 1, cn = 1, ks = 0, bn = 0, pair = 0, tpatch = 0;
+      int op = -1, patch = 0, cm = 1, cn = 1, ks = 0, bn = 0, pair = 0, tpatch = 0, dual = 0;
       if (!fgets(line, sizeof line, f) ||
-          sscanf(line, "%d %d %d %d %d %d %d %d", &op, &patch, &cm, &cn, &ks, &bn, &pair,
-                 &tpatch) < 7 ||
+          sscanf(line, "%d %d %d %d %d %d %d %d %d", &op, &patch, &cm, &cn, &ks, &bn, &pair,
+                 &tpatch, &dual) < 7 ||
           op != i) {
         found = false;
         break;
@@ -820,8 +913,17 @@ bool R2P1DModel::load_cached_plan(const char* path, int batch, cudaStream_t stre
       like.tc.tpatch = tpatch;
       std::string e;
       if (!plan_conv(i, 0, batch, false, stream, &like, &l, &e)) found = false;
+      l.dual_n_sp = dual;
+      l.dual_chunk = dual > 0 ? 4 : 0;
       plan->push_back(l);
     }
+    for (int i = 0; found && i + 1 < n; ++i)
+      if ((*plan)[i].dual_n_sp > 0) {
+        if (dual_candidate(*plan, i))
+          (*plan)[i + 1].merged = true;
+        else
+          (*plan)[i].dual_n_sp = 0;
+      }
     break;
   }
   fclose(f);
@@ -835,8 +937,8 @@ void R2P1DModel::save_cached_plan(const char* path, int batch, const std::vector
   if (!f) return;
   fprintf(f, "plan %llx %d\n", (unsigned long long)plan_key(batch), (int)plan.size());
   for (const Launch& l : plan)
-    fprintf(f, "%d %d %d %d %d %d %d %d\n", l.op, l.patch ? 1 : 0, l.tc.cm, l.tc.cn, l.tc.ks,
-            l.tc.block_n, l.patch ? l.pp.pair : l.tc.pair, l.tc.tpatch);
+    fprintf(f, "%d %d %d %d %d %d %d %d %d\n", l.op, l.patch ? 1 : 0, l.tc.cm, l.tc.cn, l.tc.ks,
+            l.tc.block_n, l.patch ? l.pp.pair : l.tc.pair, l.tc.tpatch, l.dual_n_sp);
   fclose(f);
 }
 
@@ -864,6 +966,13 @@ bool R2P1DModel::derive_plan(int batch, std::vector<Launch>* plan, std::string* 
       return false;
     plan->push_back(l);
   }
+  if (src)
+    for (int i = 0; i + 1 < (int)ops_.size(); ++i)
+      if ((*src)[i].dual_n_sp > 0 && dual_candidate(*plan, i)) {
+        (*plan)[i].dual_n_sp = (*src)[i].dual_n_sp;
+        (*plan)[i].dual_chunk = (*src)[i].dual_chunk;
+        (*plan)[i + 1].merged = true;
+      }
   return true;
 }
 
@@ -892,7 +1001,8 @@ bool R2P1DModel::plan_entry(int batch, int op, int out[7]) const {
   for (const Launch& l : it->second)
     if (l.op == op) {
       out[0] = l.patch ? 2 : (l.tc.pair ? (l.tc.tpatch ? 5 : 4) : (l.tc.ks > 1 ? 3 : 1));
-      out[1] = l.patch ? 1 : l.tc.cm;
+      if (l.dual_n_sp > 0 || l.merged) out[0] = 6;
+      out[1] = l.dual_n_sp > 0 ? l.dual_n_sp : (l.patch ? 1 : l.tc.cm);
       out[2] = l.patch ? 1 : l.tc.cn;
       out[3] = l.patch ? 0 : l.tc.ks;
       out[4] = l.patch ? l.pp.block_n : l.tc.block_n;
@@ -933,6 +1043,38 @@ int R2P1DModel::force_kernel(int batch, int op_index, int kind, int cm, int cn, 
   if (plan.size() != ops_.size()) {
     if (err) *err = "force_kernel: chunked schedules cannot be edited";
     return RNB_ESTATE;
+  }
+  if (kind == 6) {
+    // co-scheduled launch of this spatial convolution and the temporal one that follows; cm = the
+    // CTAs that start on the spatial convolution (0: three quarters of the SMs)
+    std::string e;
+    Launch a, b;
+    Launch lp;
+    lp.patch = true;
+    if (op_index + 1 >= (int)ops_.size() || !plan_conv(op_index, 0, batch, false, nullptr, &lp, &a, &e) ||
+        !plan_conv(op_index + 1, 0, batch, false, nullptr, &lp, &b, &e)) {
+      if (err) *err = ops_[op_index].name + ": the co-scheduled kernel does not apply here";
+      return RNB_EINVAL;
+    }
+    std::vector<Launch> probe = plan;
+    probe[op_index] = a;
+    probe[op_index + 1] = b;
+    if (!dual_candidate(probe, op_index)) {
+      if (err) *err = ops_[op_index].name + ": the co-scheduled kernel does not apply here";
+      return RNB_EINVAL;
+    }
+    a.dual_n_sp = cm > 0 && cm < num_sms_ ? cm : num_sms_ * 3 / 4;
+    a.dual_chunk = cn > 0 ? cn : 4;
+    b.merged = true;
+    plan[op_index] = a;
+    plan[op_index + 1] = b;
+    return RNB_OK;
+  }
+  // (pinning one half of a co-scheduled pair on its own dissolves the pair)
+  if (plan[op_index].dual_n_sp > 0 && op_index + 1 < (int)plan.size()) plan[op_index + 1].merged = false;
+  if (plan[op_index].merged && op_index > 0) {
+    plan[op_index - 1].dual_n_sp = 0;
+    plan[op_index].merged = false;
   }
   Launch like, l;
   switch (kind) {
@@ -1051,10 +1193,10 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
 
   // ---- convolutions
   if (tc) {
-    for (const Launch& l : *plan) {
-      const cudaError_t le =
-          l.patch ? launch_conv_patch(l.pp, num_sms_, stream) : launch_tc(l.tc, stream);
-      if (!cuda_ok(le, ops_[l.op].name.c_str(), err)) return RNB_ECUDA;
+    for (size_t i = 0; i < plan->size(); ++i) {
+      const Launch& l = (*plan)[i];
+      if (l.merged) continue;  // runs inside the previous, co-scheduled launch
+      if (!cuda_ok(launch_one(*plan, i, stream), ops_[l.op].name.c_str(), err)) return RNB_ECUDA;
       mark();
     }
   } else {
@@ -1107,7 +1249,12 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
   }
   if (!cuda_ok(e, "output stage", err)) return RNB_ECUDA;
   mark();
-  last_launches_ = (tc ? (int)plan->size() : (int)ops_.size()) + 2;
+  last_launches_ = 2;
+  if (tc) {
+    for (const Launch& l : *plan) last_launches_ += l.merged ? 0 : 1;
+  } else {
+    last_launches_ += (int)ops_.size();
+  }
   return RNB_OK;
 }
 

@@ -102,6 +102,7 @@ class R2P1DModel {
   void* slots_[NUM_SLOTS] = {};
   size_t slot_elems_per_clip_[NUM_SLOTS] = {};
   void* d_classify_scratch_ = nullptr;  // staged logits + arrival counter of the fused classifier
+  unsigned long long* d_dual_flags_ = nullptr;  // per-clip counters of the co-scheduled launches
   float* d_fc_w_ = nullptr;
   float* d_fc_b_ = nullptr;
   // One kernel launch of the tensor-core plan: convolution `op` over `batch` clips starting at clip
@@ -113,7 +114,16 @@ class R2P1DModel {
     bool patch = false;
     ConvTcParams tc = {};
     ConvPatchParams pp = {};
+    // Co-scheduled SpatioTemporalConv (conv_patch_dual_kernel): this (spatial, patch) launch also
+    // runs the NEXT op, the temporal convolution reading its output; `merged` marks that next
+    // entry, which is then not launched on its own.
+    int dual_n_sp = 0;   // > 0: CTAs that start on the spatial convolution
+    int dual_chunk = 0;  // temporal items per claim
+    bool merged = false;
   };
+  bool dual_candidate(const std::vector<Launch>& plan, int i) const;
+  bool tune_dual(std::vector<Launch>* plan, int i, cudaStream_t stream);
+  cudaError_t launch_one(const std::vector<Launch>& plan, size_t i, cudaStream_t stream) const;
   bool plan_conv(int op_index, int first, int batch, bool chunked, cudaStream_t stream,
                  const Launch* like, Launch* out, std::string* err, bool tune = true);
   bool build_plan(int batch, cudaStream_t stream, std::vector<Launch>* plan, std::string* err);

@@ -191,9 +191,13 @@ def test_flops_and_launch_count(engines):
     # first (N-concatenation) and last (K-concatenation) convolution of their block: 34 launches
     assert eng.num_convs == 34
     eng(R.synthetic_clips(2, seed=1).to(DEV))
-    assert eng.num_launches == 36  # 34 convolutions + input staging + pool/classifier
+    # 34 convolutions + input staging + pool/classifier; a SpatioTemporalConv whose two convolutions
+    # the plan runs as one co-scheduled launch counts once
+    duals = sum(k == 'conv_patch_dual' for *_, k in eng.op_info()) // 2
+    assert eng.num_launches == 36 - duals
     ms = eng.profile(R.synthetic_clips(16, seed=1).to(DEV))
-    assert len(ms) == 36 and all(t > 0 for t in ms)
+    duals = sum(k == 'conv_patch_dual' for *_, k in eng.op_info()) // 2
+    assert len(ms) == 36 and sum(t > 0 for t in ms) == 36 - duals
     assert sum('+shortcut' in name for name, *_ in eng.op_info()) == 6
 
 
@@ -442,7 +446,7 @@ def test_chunked_schedule_gives_identical_logits(lib, tmp_path):
         subprocess.run([sys.executable, '-c', code, path], check=True, env=env, timeout=600)
         outs.append(torch.load(path))
     (y0, n0), (y1, n1) = outs
-    assert n0 == 36 and n1 > 36
+    assert n0 <= 36 and n1 > 36
     assert torch.equal(y0, y1)
 
 

@@ -26,6 +26,7 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, 'scripts'))
 MEAN_CLIPS = (10 * 1 + 1 * 15) / 11.0   # sampler.py:58-59
+BATCH = 3                               # config/rnb.json:15; --batch overrides
 
 
 def load(name):
@@ -53,6 +54,17 @@ def make_config(kind, n):
                 for g in st['queue_groups']:
                     g['gpus'] = [0]
         return c
+    if kind == 'rnb':
+        # config/rnb.json: loaders -> LargeSmallSelector -> Batcher (1-clip videos, `batch` of them
+        # per forward) / pass-through (15-clip videos) -> runners
+        c = load('rnb.json')
+        gpus = list(range(n))
+        c['pipeline'][0]['queue_groups'][0]['gpus'] = gpus
+        c['pipeline'][1]['queue_groups'][0]['gpus'] = [0]
+        c['pipeline'][1]['queue_groups'][0]['batch'] = BATCH
+        c['pipeline'][1]['queue_groups'][1]['gpus'] = [1 if n > 1 else 0]
+        c['pipeline'][2]['queue_groups'][0]['gpus'] = gpus
+        return c
     if kind == 'segment':
         c = load('r2p1d-segment.json')
         c['pipeline'][1]['queue_groups'][0]['gpus'] = list(range(1, n)) if n > 1 else [0]
@@ -73,7 +85,7 @@ def run(kind, n, videos, mi, wire, max_clips=15, timeout=1200, runtime='referenc
     t0 = time.time()
     proc = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
                           timeout=timeout, env=env)
-    rec = {'topology': kind, 'gpus': n, 'runtime': runtime, 'videos': videos, 'mean_interval_ms': mi, 'wire': wire,
+    rec = {'topology': kind, 'gpus': n, 'runtime': runtime, 'batcher_batch': BATCH if kind == 'rnb' else None, 'videos': videos, 'mean_interval_ms': mi, 'wire': wire,
            'client': 'bulk' if mi == 0 else 'poisson', 'wall_s': time.time() - t0,
            'rc': proc.returncode}
     jobs = glob.glob(os.path.join(tmp, 'logs', '*'))
@@ -96,8 +108,11 @@ def main():
     ap.add_argument('--gpus', default='')
     ap.add_argument('--only', default='whole,aggressive,nopipeline,fourgroups,segment')
     ap.add_argument('--runtime', default='reference', choices=['reference', 'b200'])
+    ap.add_argument('--batch', type=int, default=3, help="videos per forward of the 'rnb' topology's Batcher")
     ap.add_argument('--poisson', default='', help='comma-separated mean intervals (ms) for latency runs')
     args = ap.parse_args()
+    global BATCH
+    BATCH = args.batch
     import torch
     have = torch.cuda.device_count()
     counts = [int(v) for v in args.gpus.split(',')] if args.gpus else [c for c in (1, 2, 4, 8) if c <= have]

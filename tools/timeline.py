@@ -43,8 +43,22 @@ def main():
     cupti.finalize()
     n = eng.num_launches
     assert len(recs) == n * args.steps, (len(recs), n, args.steps)
-    names = ['input staging'] + [nm for nm, *_ in eng.op_info()] + ['pool + classifier']
-    flops = [0.0] + [f * B for _, f, *_ in eng.op_info()] + [0.0]
+    names, flops = ['input staging'], [0.0]
+    info = eng.op_info()
+    k = 0
+    while k < len(info):
+        nm, f, _, _, kind = info[k]
+        if kind == 'conv_patch_dual' and k + 1 < len(info) and info[k + 1][4] == 'conv_patch_dual' \
+                and 'spatial' in nm:
+            names.append(nm.replace('.spatial_conv', '') + ' (spatial + temporal, one launch)')
+            flops.append((f + info[k + 1][1]) * B)
+            k += 2
+        else:
+            names.append(nm)
+            flops.append(f * B)
+            k += 1
+    names.append('pool + classifier')
+    flops.append(0.0)
     dur = [0.0] * n
     exp = [0.0] * n
     gap = [0.0] * n
