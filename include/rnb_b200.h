@@ -144,8 +144,8 @@ int rnb_r2p1d_num_convs(void* handle);
  * kernel the launch plan of the most recent batch size runs it with (before the first forward: the
  * kernel that applies): 0 = fp32 direct convolution, 1 = conv_tc_kernel, 2 = conv_patch_kernel,
  * 3 = conv_splitk_kernel, 4 = conv_pair_kernel, 5 = conv_pair_kernel in temporal-patch mode, 6 =
- * conv_patch_dual_kernel (reported for both convolutions of the module it runs; the second one's
- * entry in rnb_r2p1d_profile is then 0). */
+ * conv_patch_dual_kernel, 7 = conv_stem_fused_kernel (both reported for the two convolutions of the
+ * module they run in one launch; the second one's entry in rnb_r2p1d_profile is then 0). */
 int rnb_r2p1d_profile(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
                       void* stream, float* ms, int cap);
 int rnb_r2p1d_op_info(void* handle, int op, char* name, int name_cap, double* flops_per_clip,

@@ -187,6 +187,53 @@ to_stem_kernel(const In* __restrict__ in, int total_rows, Affine3 aff, uint4* __
   }
 }
 
+// Space-to-depth stem input for the fused stem kernel (conv_stem.cuh): (B, 8, 56, 56, 16) bf16,
+// channel (py * 2 + px) * 4 + c = pixel (2 h2 + py, 2 w2 + px) of colour c, slot 3 zero.  One CTA
+// per (b, t, h2): the two image rows of the three colours are read coalesced into shared memory,
+// then every thread writes one 16-byte unit (row py of one output position).
+template <typename In>
+__global__ void __launch_bounds__(128)
+to_s2d_kernel(const In* __restrict__ in, int total_rows2, Affine3 aff, uint4* __restrict__ out,
+              bool ncdhw) {
+  __shared__ float px[2][kClipC][kClipW];
+  const int r2 = blockIdx.x;  // (b * T + t) * 56 + h2
+  ptx::grid_dep_launch_dependents();
+  ptx::grid_dep_wait();  // the buffer this kernel overwrites may be an operand of the previous kernel
+  if (r2 >= total_rows2) return;
+  const int h2 = r2 % (kClipH / 2);
+  const int bt = r2 / (kClipH / 2);
+  const int t = bt % kClipT;
+  const long long b = bt / kClipT;
+  for (int i = threadIdx.x; i < 2 * kClipC * (kClipW / 4); i += blockDim.x) {
+    const int q = i % (kClipW / 4);
+    const int c = (i / (kClipW / 4)) % kClipC;
+    const int py = i / (kClipC * (kClipW / 4));
+    const int h = 2 * h2 + py;
+    const long long base = ncdhw ? ((((b * kClipC + c) * kClipT + t) * kClipH + h) * (long long)kClipW)
+                                 : ((((b * kClipT + t) * kClipC + c) * kClipH + h) * (long long)kClipW);
+    float v[4];
+    if (sizeof(In) == 1) {
+      const uchar4 u = *reinterpret_cast<const uchar4*>(in + base + 4 * q);
+      v[0] = u.x; v[1] = u.y; v[2] = u.z; v[3] = u.w;
+    } else {
+      const float4 f = *reinterpret_cast<const float4*>(in + base + 4 * q);
+      v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) px[py][c][4 * q + j] = fmaf(v[j], aff.s[c], aff.b[c]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < (kClipW / 2) * 2; i += blockDim.x) {
+    const int w2 = i >> 1, py = i & 1;
+    uint4 q;
+    q.x = pack2(px[py][0][2 * w2], px[py][1][2 * w2]);
+    q.y = pack2(px[py][2][2 * w2], 0.f);
+    q.z = pack2(px[py][0][2 * w2 + 1], px[py][1][2 * w2 + 1]);
+    q.w = pack2(px[py][2][2 * w2 + 1], 0.f);
+    out[((long long)r2 * (kClipW / 2) + w2) * 2 + py] = q;
+  }
+}
+
 // uint8 (B,T,C,H,W) -> fp32 (B,C,T,H,W); four pixels per thread
 __global__ void u8_to_f32_ncdhw_kernel(const uchar4* __restrict__ in, long long quads, Affine3 aff,
                                        float4* __restrict__ out) {
@@ -506,6 +553,22 @@ cudaError_t launch_f32_ncdhw_to_stem(const float* in, int batch, __nv_bfloat16* 
   if (rows == 0) return cudaSuccess;
   return launch_pdl(to_stem_kernel<float>, dim3((rows + kStemRows - 1) / kStemRows), dim3(256), 0, s,
                     nullptr, 0, in, rows, make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
+}
+
+cudaError_t launch_pre_u8_to_s2d(const uint8_t* in, int batch, const float* scale3,
+                                 const float* bias3, __nv_bfloat16* out, cudaStream_t s) {
+  const int rows2 = batch * kClipT * (kClipH / 2);
+  if (rows2 == 0) return cudaSuccess;
+  return launch_pdl(to_s2d_kernel<uint8_t>, dim3(rows2), dim3(128), 0, s, out,
+                    (size_t)rows2 * (kClipW / 2) * 32, in, rows2, make_affine(scale3, bias3),
+                    reinterpret_cast<uint4*>(out), false);
+}
+
+cudaError_t launch_f32_ncdhw_to_s2d(const float* in, int batch, __nv_bfloat16* out, cudaStream_t s) {
+  const int rows2 = batch * kClipT * (kClipH / 2);
+  if (rows2 == 0) return cudaSuccess;
+  return launch_pdl(to_s2d_kernel<float>, dim3(rows2), dim3(128), 0, s, nullptr, 0, in, rows2,
+                    make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
 }
 
 cudaError_t launch_pre_u8_to_f32_ncdhw(const uint8_t* in, int batch, const float* scale3,

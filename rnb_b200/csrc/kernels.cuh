@@ -42,6 +42,10 @@ cudaError_t launch_pre_u8_to_f32_ndhwc(const uint8_t* in, int batch, const float
 cudaError_t launch_pre_u8_to_bf16_ndhwc(const uint8_t* in, int batch, const float* scale3,
                                         const float* bias3, __nv_bfloat16* out, int c_pad,
                                         cudaStream_t s);
+// the same frames as the space-to-depth stem input (B, 8, 56, 56, 16) of the fused stem kernel
+cudaError_t launch_pre_u8_to_s2d(const uint8_t* in, int batch, const float* scale3,
+                                 const float* bias3, __nv_bfloat16* out, cudaStream_t s);
+cudaError_t launch_f32_ncdhw_to_s2d(const float* in, int batch, __nv_bfloat16* out, cudaStream_t s);
 // fp32 (B, 3, 8, 112, 112) (what the reference hands to the runner step) -> unfolded stem rows
 cudaError_t launch_f32_ncdhw_to_stem(const float* in, int batch, __nv_bfloat16* out, cudaStream_t s);
 

@@ -49,6 +49,8 @@ R2P1DModel::R2P1DModel(std::vector<int> layer_sizes, int start_idx, int end_idx,
   static const Dims kOut[6] = {{}, {64, 8, 56, 56}, {64, 8, 56, 56}, {128, 4, 28, 28},
                                {256, 2, 14, 14}, {512, 1, 7, 7}};
   if (const char* e = getenv("RNB_B200_FUSE_SHORTCUT")) fuse_shortcut_ = e[0] != '0';
+  stem_fused_ = dtype == RNB_DTYPE_BF16 && start_idx == 1;
+  if (const char* e = getenv("RNB_B200_STEM")) stem_fused_ = stem_fused_ && strcmp(e, "unfolded") != 0;
   in_dims_ = kIn[start_idx];
   out_dims_ = kOut[end_idx];
 }
@@ -81,6 +83,8 @@ void R2P1DModel::release() {
   d_classify_scratch_ = nullptr;
   if (d_dual_flags_) cudaFree(d_dual_flags_);
   d_dual_flags_ = nullptr;
+  if (d_stem_w_) cudaFree(d_stem_w_);
+  d_stem_w_ = nullptr;
   if (d_fc_w_) cudaFree(d_fc_w_);
   if (d_fc_b_) cudaFree(d_fc_b_);
   d_fc_w_ = d_fc_b_ = nullptr;
@@ -329,6 +333,13 @@ int R2P1DModel::finalize(std::string* err) {
               cuda_ok(cudaMalloc(&op.d_shift, np * 4), "cudaMalloc", err) &&
               cuda_ok(cudaMemcpy(op.d_scale, sc.data(), np * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err) &&
               cuda_ok(cudaMemcpy(op.d_shift, sh.data(), np * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err);
+    if (ok && stem_fused_ && &op == &ops_[0]) {
+      std::vector<uint16_t> fused;
+      pack_stem_fused_weights(op.w.data(), op.scale.data(), op.g.cout, &fused);
+      ok = cuda_ok(cudaMalloc(&d_stem_w_, fused.size() * 2), "cudaMalloc(stem weights)", err) &&
+           cuda_ok(cudaMemcpy(d_stem_w_, fused.data(), fused.size() * 2, cudaMemcpyHostToDevice),
+                   "cudaMemcpy(stem weights)", err);
+    }
     if (ok && dtype_ == RNB_DTYPE_BF16) {
       std::vector<uint16_t> packed;
       pack_conv_weights_tc(op.g, op.w.data(), op.scale.data(), &packed,
@@ -423,12 +434,14 @@ bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
   if (kernel_kind) {
     // what the launch plan of the most recent batch size chose (before any forward: what applies)
     int kind = dtype_ != RNB_DTYPE_BF16 ? 0 : (conv_patch_applicable(o.g) ? 2 : 1);
+    if (stem_fused_ && op < 2) kind = 7;
     const auto it = plans_.find(last_batch_);
     if (dtype_ == RNB_DTYPE_BF16 && it != plans_.end())
       for (const Launch& l : it->second)
         if (l.op == op) {
           kind = l.patch ? 2 : (l.tc.pair ? (l.tc.tpatch ? 5 : 4) : (l.tc.ks > 1 ? 3 : 1));
           if (l.dual_n_sp > 0 || l.merged) kind = 6;
+          if (l.stem_fused || (stem_fused_ && op < 2)) kind = 7;
           break;
         }
     *kernel_kind = kind;
@@ -723,11 +736,31 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
   return true;
 }
 
+// The two stem entries of a plan in fused mode: entry 0 runs both convolutions, entry 1 is merged.
+bool R2P1DModel::plan_stem(int batch, std::vector<Launch>* plan, std::string* err) {
+  Launch a, b;
+  a.op = 0;
+  a.batch = batch;
+  a.stem_fused = true;
+  if (!build_stem_fused_params(batch, (const __nv_bfloat16*)slots_[SLOT_U],
+                               (const __nv_bfloat16*)d_stem_w_, (const __nv_bfloat16*)ops_[1].d_w,
+                               (__nv_bfloat16*)slots_[ops_[1].out_slot], ops_[0].d_shift,
+                               ops_[1].d_shift, &a.sf, err))
+    return false;
+  b.op = 1;
+  b.batch = batch;
+  b.merged = true;
+  plan->push_back(a);
+  plan->push_back(b);
+  return true;
+}
+
 // Entry i of a plan as one launch (nothing for an entry merged into its predecessor).
 cudaError_t R2P1DModel::launch_one(const std::vector<Launch>& plan, size_t i,
                                    cudaStream_t stream) const {
   const Launch& l = plan[i];
   if (l.merged) return cudaSuccess;
+  if (l.stem_fused) return launch_conv_stem_fused(l.sf, num_sms_, stream);
   if (l.dual_n_sp > 0 && i + 1 < plan.size())
     return launch_conv_patch_dual(l.pp, plan[i + 1].pp, l.dual_n_sp, l.dual_chunk, d_dual_flags_,
                                   max_batch_, num_sms_, stream);
@@ -821,7 +854,8 @@ bool R2P1DModel::build_plan(int batch, cudaStream_t stream, std::vector<Launch>*
     return e ? atof(e) : 0.0;
   }();
   const int n = (int)ops_.size();
-  for (int i = 0; i < n; ++i) {
+  if (stem_fused_ && !plan_stem(batch, plan, err)) return false;
+  for (int i = stem_fused_ ? 2 : 0; i < n; ++i) {
     const ConvOp& op = ops_[i];
     const bool pair = i + 1 < n && op.out_slot == SLOT_M && ops_[i + 1].in_slot == SLOT_M;
     const double mid_mb_per_clip = (double)op.g.out_elems(1) * 2 / 1e6;
@@ -902,6 +936,13 @@ bool R2P1DModel::load_cached_plan(const char* path, int batch, cudaStream_t stre
         found = false;
         break;
       }
+      if (stem_fused_ && i < 2) {
+        if (i == 0) {
+          std::string e;
+          if (!plan_stem(batch, plan, &e)) found = false;
+        }
+        continue;
+      }
       Launch like, l;
       like.patch = patch != 0;
       like.tc.cm = cm;
@@ -958,7 +999,8 @@ bool R2P1DModel::derive_plan(int batch, std::vector<Launch>* plan, std::string* 
       best = d;
     }
   }
-  for (int i = 0; i < (int)ops_.size(); ++i) {
+  if (stem_fused_ && !plan_stem(batch, plan, err)) return false;
+  for (int i = stem_fused_ ? 2 : 0; i < (int)ops_.size(); ++i) {
     Launch l;
     std::string e;
     if (!(src && plan_conv(i, 0, batch, false, nullptr, &(*src)[i], &l, &e)) &&
@@ -1002,6 +1044,7 @@ bool R2P1DModel::plan_entry(int batch, int op, int out[7]) const {
     if (l.op == op) {
       out[0] = l.patch ? 2 : (l.tc.pair ? (l.tc.tpatch ? 5 : 4) : (l.tc.ks > 1 ? 3 : 1));
       if (l.dual_n_sp > 0 || l.merged) out[0] = 6;
+      if (l.stem_fused || (stem_fused_ && op < 2)) out[0] = 7;
       out[1] = l.dual_n_sp > 0 ? l.dual_n_sp : (l.patch ? 1 : l.tc.cm);
       out[2] = l.patch ? 1 : l.tc.cn;
       out[3] = l.patch ? 0 : l.tc.ks;
@@ -1036,6 +1079,10 @@ int R2P1DModel::force_kernel(int batch, int op_index, int kind, int cm, int cn, 
   }
   if (batch < 1 || batch > max_batch_ || op_index < 0 || op_index >= (int)ops_.size()) {
     if (err) *err = "force_kernel: batch or op index out of range";
+    return RNB_EINVAL;
+  }
+  if (stem_fused_ && op_index < 2) {
+    if (err) *err = "the stem runs as one fused kernel (RNB_B200_STEM=unfolded to pin its halves)";
     return RNB_EINVAL;
   }
   if (!ensure_plan(batch, nullptr, err, false)) return RNB_ECUDA;
@@ -1160,13 +1207,17 @@ int R2P1DModel::forward(const void* in, int in_fmt, int batch, void* out, int ou
   const int S_in = in_dims_.T * in_dims_.H * in_dims_.W;
   if (start_idx_ == 1) {
     if (in_fmt == RNB_FMT_U8_NTCHW) {
-      e = tc ? launch_pre_u8_to_stem((const uint8_t*)in, batch, nullptr, nullptr,
-                                     (__nv_bfloat16*)slots_[SLOT_U], stream)
+      e = tc ? (stem_fused_ ? launch_pre_u8_to_s2d((const uint8_t*)in, batch, nullptr, nullptr,
+                                                   (__nv_bfloat16*)slots_[SLOT_U], stream)
+                            : launch_pre_u8_to_stem((const uint8_t*)in, batch, nullptr, nullptr,
+                                                    (__nv_bfloat16*)slots_[SLOT_U], stream))
              : launch_pre_u8_to_f32_ndhwc((const uint8_t*)in, batch, nullptr, nullptr,
                                           (float*)slots_[SLOT_U], stream);
     } else if (in_fmt == RNB_FMT_F32_NCDHW) {
-      e = tc ? launch_f32_ncdhw_to_stem((const float*)in, batch, (__nv_bfloat16*)slots_[SLOT_U],
-                                        stream)
+      e = tc ? (stem_fused_ ? launch_f32_ncdhw_to_s2d((const float*)in, batch,
+                                                      (__nv_bfloat16*)slots_[SLOT_U], stream)
+                            : launch_f32_ncdhw_to_stem((const float*)in, batch,
+                                                       (__nv_bfloat16*)slots_[SLOT_U], stream))
              : launch_ncdhw_f32_to_ndhwc_f32((const float*)in, batch, kClipC, S_in,
                                              (float*)slots_[SLOT_U], stream);
     } else {

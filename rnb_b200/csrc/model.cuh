@@ -103,6 +103,10 @@ class R2P1DModel {
   size_t slot_elems_per_clip_[NUM_SLOTS] = {};
   void* d_classify_scratch_ = nullptr;  // staged logits + arrival counter of the fused classifier
   unsigned long long* d_dual_flags_ = nullptr;  // per-clip counters of the co-scheduled launches
+  // bf16 handles that start at layer 1 run the stem as one fused kernel on a space-to-depth input
+  // (conv_stem.cuh); RNB_B200_STEM=unfolded keeps the two patch-kernel launches of round 1
+  bool stem_fused_ = false;
+  void* d_stem_w_ = nullptr;  // spatial weights in the fused kernel's packing
   float* d_fc_w_ = nullptr;
   float* d_fc_b_ = nullptr;
   // One kernel launch of the tensor-core plan: convolution `op` over `batch` clips starting at clip
@@ -117,10 +121,15 @@ class R2P1DModel {
     // Co-scheduled SpatioTemporalConv (conv_patch_dual_kernel): this (spatial, patch) launch also
     // runs the NEXT op, the temporal convolution reading its output; `merged` marks that next
     // entry, which is then not launched on its own.
+    // Fused stem (conv_stem.cuh): this launch runs both convolutions of the stem; the next entry is
+    // `merged`.
+    bool stem_fused = false;
+    StemFusedParams sf = {};
     int dual_n_sp = 0;   // > 0: CTAs that start on the spatial convolution
     int dual_chunk = 0;  // temporal items per claim
     bool merged = false;
   };
+  bool plan_stem(int batch, std::vector<Launch>* plan, std::string* err);
   bool dual_candidate(const std::vector<Launch>& plan, int i) const;
   bool tune_dual(std::vector<Launch>* plan, int i, cudaStream_t stream);
   cudaError_t launch_one(const std::vector<Launch>& plan, size_t i, cudaStream_t stream) const;

@@ -655,6 +655,61 @@ PatchShape patch_shape(const ConvGeom& g, int pair) {
 }
 }  // namespace
 
+void pack_stem_fused_weights(const float* w, const float* scale, int cout,
+                             std::vector<uint16_t>* packed) {
+  packed->assign((size_t)kStemMid * 256, 0);
+  for (int n = 0; n < cout && n < kStemMid; ++n) {
+    const float sc = scale ? scale[n] : 1.f;
+    for (int ah = 0; ah < 4; ++ah)
+      for (int aw = 0; aw < 4; ++aw)
+        for (int py = 0; py < 2; ++py)
+          for (int px = 0; px < 2; ++px) {
+            // input row 2 ho + dh - 3 = 2 (ho + ah - 2) + py
+            const int dh = 2 * (ah - 2) + py + 3, dw = 2 * (aw - 2) + px + 3;
+            if (dh < 0 || dw < 0) continue;
+            for (int c = 0; c < 3; ++c)
+              (*packed)[(size_t)n * 256 + (ah * 4 + aw) * 16 + (py * 2 + px) * 4 + c] =
+                  f32_to_bf16_bits(w[(((size_t)n * 3 + c) * 7 + dh) * 7 + dw] * sc);
+          }
+  }
+}
+
+bool build_stem_fused_params(int B, const __nv_bfloat16* s2d, const __nv_bfloat16* w_spatial,
+                             const __nv_bfloat16* w_temporal, __nv_bfloat16* y,
+                             const float* shift_spatial, const float* shift_temporal,
+                             StemFusedParams* out, std::string* err) {
+  StemFusedParams& p = *out;
+  memset(&p, 0, sizeof p);
+  p.shift_sp = shift_spatial;
+  p.shift_tp = shift_temporal;
+  p.y = y;
+  p.B = B;
+  {
+    // dimension order (c, w, t, h, b): the box then lies in shared memory as rows h * 128 + t * 16 + w
+    const uint64_t row = (uint64_t)kStemS2dC * 2, plane = (uint64_t)kStemHW * kStemHW * row;
+    const uint64_t dims[5] = {(uint64_t)kStemS2dC, (uint64_t)kStemHW, (uint64_t)kStemT,
+                              (uint64_t)kStemHW, (uint64_t)B};
+    const uint64_t strides[4] = {row, plane, (uint64_t)kStemHW * row, (uint64_t)kStemT * plane};
+    const uint32_t box[5] = {(uint32_t)kStemS2dC, 16u, (uint32_t)kStemT, 4u, 1u};
+    if (!encode_bf16(&p.in_map, s2d, 5, dims, strides, box, 32, err)) return false;
+  }
+  {
+    const uint64_t dims[2] = {256, (uint64_t)kStemMid};
+    const uint64_t strides[1] = {512};
+    const uint32_t box[2] = {16u, (uint32_t)kStemMid};
+    if (!encode_bf16(&p.wsp_map, w_spatial, 2, dims, strides, box, 32, err)) return false;
+  }
+  {
+    const uint64_t dims[2] = {3 * (uint64_t)kStemMid, (uint64_t)kStemOut};
+    const uint64_t strides[1] = {3 * (uint64_t)kStemMid * 2};
+    const uint32_t box[2] = {64u, (uint32_t)kStemOut};
+    if (!encode_bf16(&p.wtp_map, w_temporal, 2, dims, strides, box, 128, err)) return false;
+    const uint32_t tbox[2] = {32u, (uint32_t)kStemOut};
+    if (!encode_bf16(&p.wtp_tail_map, w_temporal, 2, dims, strides, tbox, 64, err)) return false;
+  }
+  return true;
+}
+
 bool conv_patch_applicable(const ConvGeom& g, int pair) { return patch_shape(g, pair).ok; }
 bool conv_patch_streams(const ConvGeom& g, int pair) {
   const PatchShape s = patch_shape(g, pair);

@@ -5,6 +5,7 @@
 #include <vector>
 
 #include "conv_patch.cuh"
+#include "conv_stem.cuh"
 #include "conv_tc.cuh"
 
 namespace rnb {
@@ -100,6 +101,16 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                              const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                              const __nv_bfloat16* residual, bool relu, ConvPatchParams* out,
                              std::string* err, int pair = 0);
+
+// Fused stem (conv_stem.cuh).  Spatial weights: torch (cout, 3, 1, 7, 7) fp32 -> K-major bf16 rows
+// (96, 256), K = (4x4 tap of the space-to-depth filter) x 16 channel slots, rows scaled by the
+// folded BatchNorm.  The temporal weights use pack_conv_weights_tc (64 rows x 3 x 96).
+void pack_stem_fused_weights(const float* w, const float* scale, int cout,
+                             std::vector<uint16_t>* packed);
+bool build_stem_fused_params(int B, const __nv_bfloat16* s2d, const __nv_bfloat16* w_spatial,
+                             const __nv_bfloat16* w_temporal, __nv_bfloat16* y,
+                             const float* shift_spatial, const float* shift_temporal,
+                             StemFusedParams* out, std::string* err);
 
 uint16_t f32_to_bf16_bits(float f);
 float bf16_bits_to_f32(uint16_t b);

@@ -151,6 +151,30 @@ def test_batch_invariance_without_splitk(lib, tmp_path):
     assert torch.equal(y1, y16[3:4])
 
 
+def test_stem_fused_and_unfolded_agree(lib, monkeypatch):
+    """The stem as one fused kernel on a space-to-depth input (default) and as two patch-kernel
+    launches on the unfolded layout (RNB_B200_STEM=unfolded): both against the oracle's conv1 output
+    (network.py:22), from uint8 frames and from the fp32 tensor the runner step receives."""
+    from rnb_b200.engine import R2P1DEngine
+    m = R.build(1, 1, seed=3, harden=True)
+    clips = R.synthetic_clips(3, seed=17)
+    x = R.preprocess(clips).contiguous()
+    want = R.forward(m, x)
+    outs = {}
+    for mode in ('fused', 'unfolded'):
+        monkeypatch.setenv('RNB_B200_STEM', mode)
+        eng = R2P1DEngine(DEV, m.state_dict(), 1, 1, dtype='bf16', max_batch=3).prepare(3)
+        kinds = [k for *_, k in eng.op_info()]
+        assert kinds == (['conv_stem_fused'] * 2 if mode == 'fused' else ['conv_patch'] * 2), kinds
+        a = eng(clips.to(DEV)).cpu().clone()
+        b = eng(x.to(DEV)).cpu().clone()
+        assert torch.equal(a, b)
+        assert float(rel_err_per_clip(a, want).max()) <= TOL['bf16']
+        outs[mode] = a
+        eng.close()
+    assert float(rel_err_per_clip(outs['fused'], outs['unfolded']).max()) <= TOL['bf16'] / 4
+
+
 @pytest.mark.parametrize('dtype', ['bf16', 'fp32'])
 @pytest.mark.parametrize('start,end', [(1, 1), (2, 2), (3, 3), (4, 4), (3, 4), (5, 5), (2, 5)])
 def test_layer_ranges(lib, dtype, start, end):
@@ -193,11 +217,13 @@ def test_flops_and_launch_count(engines):
     eng(R.synthetic_clips(2, seed=1).to(DEV))
     # 34 convolutions + input staging + pool/classifier; a SpatioTemporalConv whose two convolutions
     # the plan runs as one co-scheduled launch counts once
-    duals = sum(k == 'conv_patch_dual' for *_, k in eng.op_info()) // 2
+    one_launch = ('conv_patch_dual', 'conv_stem_fused')
+    duals = sum(k in one_launch for *_, k in eng.op_info()) // 2
     assert eng.num_launches == 36 - duals
     ms = eng.profile(R.synthetic_clips(16, seed=1).to(DEV))
-    duals = sum(k == 'conv_patch_dual' for *_, k in eng.op_info()) // 2
+    duals = sum(k in one_launch for *_, k in eng.op_info()) // 2
     assert len(ms) == 36 and sum(t > 0 for t in ms) == 36 - duals
+    assert [k for *_, k in eng.op_info()][:2] == ['conv_stem_fused'] * 2   # the default stem
     assert sum('+shortcut' in name for name, *_ in eng.op_info()) == 6
 
 

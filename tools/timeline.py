@@ -48,8 +48,8 @@ def main():
     k = 0
     while k < len(info):
         nm, f, _, _, kind = info[k]
-        if kind == 'conv_patch_dual' and k + 1 < len(info) and info[k + 1][4] == 'conv_patch_dual' \
-                and 'spatial' in nm:
+        if kind in ('conv_patch_dual', 'conv_stem_fused') and k + 1 < len(info) \
+                and info[k + 1][4] == kind and 'spatial' in nm:
             names.append(nm.replace('.spatial_conv', '') + ' (spatial + temporal, one launch)')
             flops.append((f + info[k + 1][1]) * B)
             k += 2
