@@ -9,6 +9,12 @@
 // filter then is a stride-1 4x4 filter over (h2, w2) with K = 16 per tap (taps that would need
 // filter row / column -1 carry zero weights).
 //
+// Both per-channel shifts ride in the GEMMs, so the epilogues only clamp and convert: slot 3 of
+// pixel (py, px) = (0, 0) holds the constant 1 and the spatial weight row of that slot at the
+// centre tap holds the folded BatchNorm shift; channel 95 of the intermediate (padding: 83 real
+// channels) is written as 1 and the temporal weights of that channel at the centre tap hold the
+// bias.  (The shifts are thereby rounded to bf16, like the weights.)
+//
 // Tile: one output row, kStemTw output columns, all 8 frames = 128 accumulator rows ordered
 // (t, column) with a column pitch of 16.  The patch (4 s2d rows x 16 columns x 8 frames, fetched by
 // one TMA box whose dimensions are ordered (c, w, t, h)) lies in shared memory as rows
@@ -37,14 +43,12 @@ struct StemFusedParams {
   alignas(64) CUtensorMap wsp_map;       // spatial weights (K = 256, N = 96), box (16, 96), 32-B swizzle
   alignas(64) CUtensorMap wtp_map;       // temporal weights (K = 288, N = 64), box (64, 64), 128-B swizzle
   alignas(64) CUtensorMap wtp_tail_map;  // same tensor, box (32, 64), 64-B swizzle (channels 64..95)
-  const float* shift_sp;                 // [96] folded BatchNorm shift of the spatial convolution
-  const float* shift_tp;                 // [64] bias of the temporal convolution
   __nv_bfloat16* y;                      // (B, 8, 56, 56, 64)
   int B;
 };
 
 constexpr int kStemFusedSmem = 1024 /*align*/ + 1024 /*control*/ + 16 * kStemMid * 32 +
-                               3 * kStemOut * 128 + 3 * kStemOut * 64 + 3 * 16384 + 1024 +
+                               3 * kStemOut * 128 + 3 * kStemOut * 64 + 4 * 16384 + 1024 +
                                2 * (160 * 128 + 160 * 64);
 
 cudaError_t launch_conv_stem_fused(const StemFusedParams& p, int num_sms, cudaStream_t stream);

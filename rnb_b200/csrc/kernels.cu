@@ -188,7 +188,8 @@ to_stem_kernel(const In* __restrict__ in, int total_rows, Affine3 aff, uint4* __
 }
 
 // Space-to-depth stem input for the fused stem kernel (conv_stem.cuh): (B, 8, 56, 56, 16) bf16,
-// channel (py * 2 + px) * 4 + c = pixel (2 h2 + py, 2 w2 + px) of colour c, slot 3 zero.  One CTA
+// channel (py * 2 + px) * 4 + c = pixel (2 h2 + py, 2 w2 + px) of colour c; slot 3 is zero except
+// for pixel (0, 0), where it holds the constant 1 (conv_stem.cuh).  One CTA
 // per (b, t, h2): the two image rows of the three colours are read coalesced into shared memory,
 // then every thread writes one 16-byte unit (row py of one output position).
 template <typename In>
@@ -196,10 +197,10 @@ __global__ void __launch_bounds__(128)
 to_s2d_kernel(const In* __restrict__ in, int total_rows2, Affine3 aff, uint4* __restrict__ out,
               bool ncdhw) {
   __shared__ float px[2][kClipC][kClipW];
-  const int r2 = blockIdx.x;  // (b * T + t) * 56 + h2
   ptx::grid_dep_launch_dependents();
   ptx::grid_dep_wait();  // the buffer this kernel overwrites may be an operand of the previous kernel
-  if (r2 >= total_rows2) return;
+  for (int r2 = blockIdx.x; r2 < total_rows2; r2 += gridDim.x) {  // r2 = (b * T + t) * 56 + h2
+  if (r2 != (int)blockIdx.x) __syncthreads();  // the previous row pair has been read out
   const int h2 = r2 % (kClipH / 2);
   const int bt = r2 / (kClipH / 2);
   const int t = bt % kClipT;
@@ -227,10 +228,12 @@ to_s2d_kernel(const In* __restrict__ in, int total_rows2, Affine3 aff, uint4* __
     const int w2 = i >> 1, py = i & 1;
     uint4 q;
     q.x = pack2(px[py][0][2 * w2], px[py][1][2 * w2]);
-    q.y = pack2(px[py][2][2 * w2], 0.f);
+    // slot 3 of pixel (py, px) = (0, 0): the constant one that carries the BatchNorm shift
+    q.y = pack2(px[py][2][2 * w2], py == 0 ? 1.f : 0.f);
     q.z = pack2(px[py][0][2 * w2 + 1], px[py][1][2 * w2 + 1]);
     q.w = pack2(px[py][2][2 * w2 + 1], 0.f);
     out[((long long)r2 * (kClipW / 2) + w2) * 2 + py] = q;
+  }
   }
 }
 
@@ -555,11 +558,14 @@ cudaError_t launch_f32_ncdhw_to_stem(const float* in, int batch, __nv_bfloat16* 
                     nullptr, 0, in, rows, make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
 }
 
+// grid of the space-to-depth staging kernel: a few row pairs per CTA once there are many
+static inline int s2d_grid(int rows2) { return rows2; }  // (several row pairs per CTA: slower)
+
 cudaError_t launch_pre_u8_to_s2d(const uint8_t* in, int batch, const float* scale3,
                                  const float* bias3, __nv_bfloat16* out, cudaStream_t s) {
   const int rows2 = batch * kClipT * (kClipH / 2);
   if (rows2 == 0) return cudaSuccess;
-  return launch_pdl(to_s2d_kernel<uint8_t>, dim3(rows2), dim3(128), 0, s, out,
+  return launch_pdl(to_s2d_kernel<uint8_t>, dim3(s2d_grid(rows2)), dim3(128), 0, s, out,
                     (size_t)rows2 * (kClipW / 2) * 32, in, rows2, make_affine(scale3, bias3),
                     reinterpret_cast<uint4*>(out), false);
 }
@@ -567,7 +573,7 @@ cudaError_t launch_pre_u8_to_s2d(const uint8_t* in, int batch, const float* scal
 cudaError_t launch_f32_ncdhw_to_s2d(const float* in, int batch, __nv_bfloat16* out, cudaStream_t s) {
   const int rows2 = batch * kClipT * (kClipH / 2);
   if (rows2 == 0) return cudaSuccess;
-  return launch_pdl(to_s2d_kernel<float>, dim3(rows2), dim3(128), 0, s, nullptr, 0, in, rows2,
+  return launch_pdl(to_s2d_kernel<float>, dim3(s2d_grid(rows2)), dim3(128), 0, s, nullptr, 0, in, rows2,
                     make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
 }
 

@@ -335,7 +335,7 @@ int R2P1DModel::finalize(std::string* err) {
               cuda_ok(cudaMemcpy(op.d_shift, sh.data(), np * 4, cudaMemcpyHostToDevice), "cudaMemcpy", err);
     if (ok && stem_fused_ && &op == &ops_[0]) {
       std::vector<uint16_t> fused;
-      pack_stem_fused_weights(op.w.data(), op.scale.data(), op.g.cout, &fused);
+      pack_stem_fused_weights(op.w.data(), op.scale.data(), op.shift.data(), op.g.cout, &fused);
       ok = cuda_ok(cudaMalloc(&d_stem_w_, fused.size() * 2), "cudaMalloc(stem weights)", err) &&
            cuda_ok(cudaMemcpy(d_stem_w_, fused.data(), fused.size() * 2, cudaMemcpyHostToDevice),
                    "cudaMemcpy(stem weights)", err);
@@ -347,6 +347,9 @@ int R2P1DModel::finalize(std::string* err) {
                            op.scale_extra.empty() ? nullptr : op.scale_extra.data(),
                            op.w_ncat.empty() ? nullptr : op.w_ncat.data(),
                            op.scale_ncat.empty() ? nullptr : op.scale_ncat.data());
+      // fused stem: the temporal bias rides in the GEMM (conv_stem.cuh)
+      if (stem_fused_ && &op == &ops_[1])
+        stem_fused_add_temporal_bias(op.shift.data(), op.g.cout, &packed);
       ok = cuda_ok(cudaMalloc(&op.d_w, packed.size() * 2), "cudaMalloc(weights)", err) &&
            cuda_ok(cudaMemcpy(op.d_w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice),
                    "cudaMemcpy(weights)", err);
@@ -744,8 +747,7 @@ bool R2P1DModel::plan_stem(int batch, std::vector<Launch>* plan, std::string* er
   a.stem_fused = true;
   if (!build_stem_fused_params(batch, (const __nv_bfloat16*)slots_[SLOT_U],
                                (const __nv_bfloat16*)d_stem_w_, (const __nv_bfloat16*)ops_[1].d_w,
-                               (__nv_bfloat16*)slots_[ops_[1].out_slot], ops_[0].d_shift,
-                               ops_[1].d_shift, &a.sf, err))
+                               (__nv_bfloat16*)slots_[ops_[1].out_slot], &a.sf, err))
     return false;
   b.op = 1;
   b.batch = batch;

@@ -655,11 +655,19 @@ PatchShape patch_shape(const ConvGeom& g, int pair) {
 }
 }  // namespace
 
-void pack_stem_fused_weights(const float* w, const float* scale, int cout,
+void stem_fused_add_temporal_bias(const float* bias, int cout, std::vector<uint16_t>* packed) {
+  // row n, centre tap (dt = 1), channel 95 = the constant-one channel of the intermediate
+  for (int n = 0; n < cout && n < kStemOut; ++n)
+    (*packed)[(size_t)n * 3 * kStemMid + kStemMid + (kStemMid - 1)] = f32_to_bf16_bits(bias[n]);
+}
+
+void pack_stem_fused_weights(const float* w, const float* scale, const float* shift, int cout,
                              std::vector<uint16_t>* packed) {
   packed->assign((size_t)kStemMid * 256, 0);
   for (int n = 0; n < cout && n < kStemMid; ++n) {
     const float sc = scale ? scale[n] : 1.f;
+    // centre tap (ah, aw) = (2, 2), slot 3 of pixel (0, 0): multiplies the constant one
+    if (shift) (*packed)[(size_t)n * 256 + (2 * 4 + 2) * 16 + 3] = f32_to_bf16_bits(shift[n]);
     for (int ah = 0; ah < 4; ++ah)
       for (int aw = 0; aw < 4; ++aw)
         for (int py = 0; py < 2; ++py)
@@ -676,12 +684,9 @@ void pack_stem_fused_weights(const float* w, const float* scale, int cout,
 
 bool build_stem_fused_params(int B, const __nv_bfloat16* s2d, const __nv_bfloat16* w_spatial,
                              const __nv_bfloat16* w_temporal, __nv_bfloat16* y,
-                             const float* shift_spatial, const float* shift_temporal,
                              StemFusedParams* out, std::string* err) {
   StemFusedParams& p = *out;
   memset(&p, 0, sizeof p);
-  p.shift_sp = shift_spatial;
-  p.shift_tp = shift_temporal;
   p.y = y;
   p.B = B;
   {

@@ -104,12 +104,14 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
 
 // Fused stem (conv_stem.cuh).  Spatial weights: torch (cout, 3, 1, 7, 7) fp32 -> K-major bf16 rows
 // (96, 256), K = (4x4 tap of the space-to-depth filter) x 16 channel slots, rows scaled by the
-// folded BatchNorm.  The temporal weights use pack_conv_weights_tc (64 rows x 3 x 96).
-void pack_stem_fused_weights(const float* w, const float* scale, int cout,
+// folded BatchNorm, plus the shift itself in the constant-one slot of the centre tap.  The temporal
+// weights are pack_conv_weights_tc's (64 rows x 3 x 96) with the bias added in the constant-one
+// channel of the centre tap (stem_fused_add_temporal_bias).
+void pack_stem_fused_weights(const float* w, const float* scale, const float* shift, int cout,
                              std::vector<uint16_t>* packed);
+void stem_fused_add_temporal_bias(const float* bias, int cout, std::vector<uint16_t>* packed);
 bool build_stem_fused_params(int B, const __nv_bfloat16* s2d, const __nv_bfloat16* w_spatial,
                              const __nv_bfloat16* w_temporal, __nv_bfloat16* y,
-                             const float* shift_spatial, const float* shift_temporal,
                              StemFusedParams* out, std::string* err);
 
 uint16_t f32_to_bf16_bits(float f);

@@ -172,7 +172,7 @@ def test_stem_fused_and_unfolded_agree(lib, monkeypatch):
         assert float(rel_err_per_clip(a, want).max()) <= TOL['bf16']
         outs[mode] = a
         eng.close()
-    assert float(rel_err_per_clip(outs['fused'], outs['unfolded']).max()) <= TOL['bf16'] / 4
+    assert float(rel_err_per_clip(outs['fused'], outs['unfolded']).max()) <= TOL['bf16'] / 2
 
 
 @pytest.mark.parametrize('dtype', ['bf16', 'fp32'])
