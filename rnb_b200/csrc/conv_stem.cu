@@ -1,13 +1,14 @@
 // Fused stem kernel (see conv_stem.cuh).
 //
-//   warp 0      TMA producer: both weight sets once, then one patch (16 KB) per tile, ring of 3
-//   warp 1      MMA issuer (warp-wide, one elected lane issues): spatial accumulator S of tile i+1,
+//   warp 0      TMA producer: both weight sets once, then one patch (16 KB) per tile, ring of 4
+//   warp 1      MMA issuer (warp-wide, one elected lane issues): spatial accumulator S of tile i+2,
 //               then the temporal accumulator Y of tile i -- so the tensor core works on the next
-//               tile's 4x4 taps while the intermediate of this tile is being converted
-//   warps 2-5   "mid" epilogue: S (TMEM) -> + shift -> ReLU -> bf16 -> shared-memory operand of the
-//               temporal convolution (128-byte-swizzled block of channels 0..63, 64-byte-swizzled
-//               block of channels 64..95), proxy fence, hand over to the MMA warp
-//   warps 6-9   output epilogue: Y (TMEM) -> + bias -> bf16 -> 32-byte global stores
+//               tiles' 4x4 taps while the intermediate of this tile is being converted
+//   warps 2-5   "mid" epilogue: S (TMEM) -> ReLU -> bf16 -> shared-memory operand of the temporal
+//               convolution (128-byte-swizzled block of channels 0..63, 64-byte-swizzled block of
+//               channels 64..95), proxy fence, hand over to the MMA warp
+//   warps 6-9   output epilogue: Y (TMEM) -> bf16 -> 32-byte global stores
+//   (the BatchNorm shift and the bias are weight rows of the two GEMMs, see conv_stem.cuh)
 #include "conv_stem.cuh"
 
 #include <atomic>
@@ -53,8 +54,8 @@ conv_stem_fused_kernel(const __grid_constant__ StemFusedParams p) {
 
   // control block
   const uint32_t w_full = base;
-  const uint32_t p_full = base + 8;                 // [3]
-  const uint32_t p_empty = p_full + 8 * kPatchBufs;  // [3]
+  const uint32_t p_full = base + 8;                 // [kPatchBufs]
+  const uint32_t p_empty = p_full + 8 * kPatchBufs;  // [kPatchBufs]
   const uint32_t s_full = p_empty + 8 * kPatchBufs;  // [kSBufs]
   const uint32_t s_empty = s_full + 8 * kSBufs;
   const uint32_t m_full = s_empty + 8 * kSBufs;

@@ -5,7 +5,7 @@
 // room for that; the two-kernel path moves 77 MB of intermediate out to HBM and back at batch 16.
 //
 // Input layout "space to depth": (B, 8, 56, 56, 16) bf16, channel = (py * 2 + px) * 4 + c holding
-// input pixel (2 h2 + py, 2 w2 + px) of colour c (slot 3 of every pixel is zero).  The stride-2 7x7
+// input pixel (2 h2 + py, 2 w2 + px) of colour c (slot 3 is zero but for pixel (0, 0)).  The stride-2 7x7
 // filter then is a stride-1 4x4 filter over (h2, w2) with K = 16 per tap (taps that would need
 // filter row / column -1 carry zero weights).
 //
@@ -20,7 +20,7 @@
 // one TMA box whose dimensions are ordered (c, w, t, h)) lies in shared memory as rows
 // h * 128 + t * 16 + w, so filter tap (ah, aw) is the 128 consecutive rows from ah * 128 + aw on:
 // a row offset in the UMMA descriptor, as in conv_patch.cu.  The spatial accumulator goes through
-// shift + ReLU into a second shared-memory operand of 10 frames x 16 rows (zero frames at both
+// ReLU into a second shared-memory operand of 10 frames x 16 rows (zero frames at both
 // ends = the temporal padding), where temporal tap dt is the rows from dt * 16 on.
 #pragma once
 #include <cuda.h>
