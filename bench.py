@@ -501,7 +501,8 @@ def main():
         cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1',
                '--nproc-per-node', str(args.gpus), '--master-addr', '127.0.0.1',
                '--master-port', str(port), os.path.abspath(__file__)] + sys.argv[1:]
-        sys.exit(subprocess.call(cmd))
+        # (this process's fd 1 already points at stderr; hand the workers the real stdout)
+        sys.exit(subprocess.call(cmd, stdout=_REAL_STDOUT))
     if args.impl == 'reference':
         run_reference(args, rank)
     else:
