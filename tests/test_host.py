@@ -194,3 +194,79 @@ def test_configs_name_importable_classes():
         for p in paths:
             mod, cls = p.rsplit('.', 1)
             assert hasattr(importlib.import_module(mod), cls), p
+
+
+def test_tensor_event_on_the_host_has_the_reference_attributes():
+    """control.TensorEvent's attributes (control.py:40-46) plus a dtype per tensor; no CUDA needed
+    for a CPU buffer (the aggregator of r2p1d-segment.json lives on the host)."""
+    from rnb_b200 import handoff
+    te = handoff.TensorEvent(((5, 400), (5, 8, 3, 112, 112)), 'cpu', dtype=(torch.float32, torch.uint8))
+    assert [t.dtype for t in te.tensors] == [torch.float32, torch.uint8]
+    assert [tuple(t.shape) for t in te.tensors] == [(5, 400), (5, 8, 3, 112, 112)]
+    assert te.event.is_set() and len(te.valid_batch_sizes) == 2
+    assert te.ready is None and te.free is None
+    with pytest.raises(ValueError):
+        handoff.TensorEvent(((5, 400),), 'cpu', dtype=(torch.float32, torch.uint8))
+
+
+def test_wire_format_of_the_step_classes(monkeypatch):
+    """RNB_B200_WIRE decides, statically, what the loader puts on the wire (control.py:125-131
+    evaluates output_shape() in the main process)."""
+    import importlib
+    from rnb_b200 import steps
+    assert steps.R2P1DLoader.output_shape() == ((steps.MAX_CLIPS, 3, 8, 112, 112),)
+    assert steps.R2P1DLoader.output_dtype() == (torch.float32,)
+    monkeypatch.setenv('RNB_B200_WIRE', 'uint8')
+    try:
+        importlib.reload(steps)
+        assert steps.R2P1DLoader.output_shape() == ((steps.MAX_CLIPS, 8, 3, 112, 112),)
+        assert steps.R2P1DLoader.output_dtype() == (torch.uint8,)
+        assert steps.Batcher.output_dtype() == (torch.uint8,)
+    finally:
+        monkeypatch.delenv('RNB_B200_WIRE')
+        importlib.reload(steps)
+    assert steps._default_prepare_batches(64) == sorted({1, 3, 4, 5, 10, 15, steps.MAX_CLIPS})
+
+
+def test_latency_percentiles_from_a_timecard_log(tmp_path):
+    """scripts/latency_percentiles.py on a log in the reference's format (rnb_logging.py:188-214,
+    benchmark.py:297-300): latency = last stamp - enqueue_filename."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, 'scripts'))
+    import latency_percentiles
+    job = tmp_path / 'logs' / 'job'
+    job.mkdir(parents=True)
+    rows = ['enqueue_filename runner0_start inference0_start inference0_finish gpu0']
+    for i in range(100):
+        t0 = 1000.0 + i * 0.01
+        rows.append('%f %f %f %f 0' % (t0, t0 + 0.001, t0 + 0.002, t0 + 0.002 + 0.001 * (i + 1)))
+    (job / 'g0-group0-0.txt').write_text('\n'.join(rows) + '\n')
+    (job / 'log-meta.txt').write_text(
+        "Args: Namespace(mean_interval_ms=0, batch_size=1, videos=100, queue_size=50000)\n"
+        "1000.000000 1002.000000\nTermination flag: 0\n")
+    out = latency_percentiles.parse_job(str(job), skip=0)
+    assert out['videos_logged'] == 100 and out['termination_flag'] == 0
+    assert abs(out['videos_per_s'] - 50.0) < 1e-6
+    assert abs(out['latency_ms']['p50'] - (2 + 51)) < 1e-3      # 51st of 1..100 ms on top of 2 ms
+    assert abs(out['latency_ms']['p99'] - (2 + 100)) < 1e-3
+    assert out['keys'][0] == 'enqueue_filename'
+
+
+def test_harness_topologies_are_valid_pipelines():
+    """tools/harness_sweep.py cuts the config/*.json mirrors down to N GPUs; the result must still
+    satisfy the checks of the reference's sanity_check (benchmark.py:46-91)."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, 'tools'))
+    import harness_sweep
+    for kind, n in [('whole', 1), ('aggressive', 2), ('aggressive', 8), ('nopipeline', 4),
+                    ('fourgroups', 1), ('fourgroups', 4), ('segment', 4), ('rnb', 1), ('rnb', 8)]:
+        cfg = harness_sweep.make_config(kind, n)
+        out_queues = None
+        for i, step in enumerate(cfg['pipeline']):
+            assert isinstance(step['model'], str) and step['model'].startswith('rnb_b200.steps.')
+            gpus = [g for grp in step['queue_groups'] for g in grp['gpus']]
+            assert gpus and all(g < max(n, 1) for g in gpus)
+            if i > 0:
+                assert set(g['in_queue'] for g in step['queue_groups']) == out_queues
+            if i < len(cfg['pipeline']) - 1:
+                out_queues = set(q for g in step['queue_groups'] for q in g['out_queues'])
