@@ -91,7 +91,8 @@ int rnb_r2p1d_prepare(void* handle, int batch, void* stream);
  * channel tile <= block_n, 4 = conv_pair_kernel with channel tile <= block_n, 5 = conv_pair_kernel
  * in temporal-patch mode, 6 = conv_patch_dual_kernel: ONE launch for the 1 x k x k convolution `op`
  * and the k x 1 x 1 convolution op + 1 of the same SpatioTemporalConv, with cm CTAs starting on the
- * spatial half (0: three quarters of the SMs) and cn temporal tiles per claim (0: 4).  RNB_EINVAL if
+ * spatial half (0: three quarters of the SMs) and cn temporal tiles per claim (0: 4), 8 =
+ * conv_tsum_kernel (3 x 1 x 1 layers of 8-frame clips with 64 output channels).  RNB_EINVAL if
  * that kernel or shape does not apply to the layer. */
 int rnb_r2p1d_force_kernel(void* handle, int batch, int op, int kind, int cm, int cn, int ks,
                            int block_n, int pair);
@@ -145,7 +146,8 @@ int rnb_r2p1d_num_convs(void* handle);
  * kernel that applies): 0 = fp32 direct convolution, 1 = conv_tc_kernel, 2 = conv_patch_kernel,
  * 3 = conv_splitk_kernel, 4 = conv_pair_kernel, 5 = conv_pair_kernel in temporal-patch mode, 6 =
  * conv_patch_dual_kernel, 7 = conv_stem_fused_kernel (both reported for the two convolutions of the
- * module they run in one launch; the second one's entry in rnb_r2p1d_profile is then 0). */
+ * module they run in one launch; the second one's entry in rnb_r2p1d_profile is then 0), 8 =
+ * conv_tsum_kernel (3x1x1 layers of 8-frame clips, filter taps stacked along the output columns). */
 int rnb_r2p1d_profile(void* handle, const void* in, int in_fmt, int batch, void* out, int out_fmt,
                       void* stream, float* ms, int cap);
 int rnb_r2p1d_op_info(void* handle, int op, char* name, int name_cap, double* flops_per_clip,

@@ -41,6 +41,7 @@ __device__ __forceinline__ PatchItem decode_patch_item(const ConvPatchParams& p,
   tile /= p.tiles_h;
   const int it = tile % p.tiles_t;
   c.b = tile / p.tiles_t;
+  if (p.reverse && c.b < p.tiles_b) c.b = p.tiles_b - 1 - c.b;
   c.w0 = iw * p.tw;
   c.h0 = ih * p.th;
   c.t0 = it * p.tt;

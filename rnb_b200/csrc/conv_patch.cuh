@@ -55,6 +55,10 @@ struct ConvPatchParams {
 #endif
   int res_smem;
   int pair;             // 1: CTA pairs (cta_group::2), each CTA holds half of every weight tile
+  // 1: clips are taken last to first.  A kernel whose input was written first-to-last by the launch
+  // before it finds the clips written LAST still in L2 (the 115 MB conv2 intermediate does not fit
+  // as a whole), so consecutive launches alternate the direction; results do not depend on it.
+  int reverse;
   // output tile: tw x th x tt positions, laid out in the accumulator with power-of-two pitches
   int tw, th, tt;
   int lpw, lph;         // log2 of the row pitches: row = (t << (lpw + lph)) + (h << lpw) + w

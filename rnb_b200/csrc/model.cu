@@ -443,6 +443,7 @@ bool R2P1DModel::op_info(int op, std::string* name, double* flops_per_clip,
       for (const Launch& l : it->second)
         if (l.op == op) {
           kind = l.patch ? 2 : (l.tc.pair ? (l.tc.tpatch ? 5 : 4) : (l.tc.ks > 1 ? 3 : 1));
+          if (l.tsum) kind = 8;
           if (l.dual_n_sp > 0 || l.merged) kind = 6;
           if (l.stem_fused || (stem_fused_ && op < 2)) kind = 7;
           break;
@@ -527,6 +528,13 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
     if (err) *err = op.name + ": " + m;
     return false;
   };
+  if (like && like->tsum) {
+    out->patch = false;
+    out->tsum = true;
+    return build_conv_tsum_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &out->ts, &perr)
+               ? true
+               : fail(perr);
+  }
   if (like) {
     out->patch = like->patch;
     const bool ok = like->patch
@@ -549,9 +557,50 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
   const bool patch_only = patch_ok && !conv_patch_streams(op.g);
   if (patch_only) {
     out->patch = true;
-    return build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &out->pp, &perr)
-               ? true
-               : fail(perr);
+    if (!build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &out->pp, &perr))
+      return fail(perr);
+    // 3x1x1 layers of 8-frame clips: the taps-along-N kernel (conv_tsum.cuh).  Measured equal to
+    // the patch kernel within 1-2 % in the real step (profiles/r02_conv_tsum.md: both designs load
+    // the SM's shared-memory data pipe about equally), and its fp32 summation order differs, so it
+    // is opt-in: RNB_B200_TSUM=1 takes it wherever it applies, RNB_B200_TSUM=time lets the timing
+    // decide, anything else (the default) keeps the patch kernel.
+    static const int tsum_mode = [] {
+      const char* e = getenv("RNB_B200_TSUM");
+      return !e ? 0 : (e[0] == '1' ? 1 : (e[0] == 't' ? -1 : 0));
+    }();
+    ConvTsumParams ts;
+    std::string terr;
+    if (tsum_mode != 0 && (tune || tsum_mode == 1) && conv_tsum_applicable(op.g) &&
+        build_conv_tsum_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &ts, &terr)) {
+      bool use = tsum_mode == 1;
+      cudaEvent_t e0, e1;
+      if (!use && cudaEventCreate(&e0) == cudaSuccess) {
+        if (cudaEventCreate(&e1) == cudaSuccess) {
+          auto time_it = [&](auto&& launch, float* ms) -> bool {
+            cudaError_t te = launch();
+            if (te == cudaSuccess) te = cudaEventRecord(e0, stream);
+            for (int r = 0; r < 8 && te == cudaSuccess; ++r) te = launch();
+            if (te == cudaSuccess) te = cudaEventRecord(e1, stream);
+            if (te == cudaSuccess) te = cudaEventSynchronize(e1);
+            if (te == cudaSuccess) te = cudaEventElapsedTime(ms, e0, e1);
+            if (te != cudaSuccess) (void)cudaGetLastError();
+            return te == cudaSuccess;
+          };
+          float ms_patch = 0.f, ms_tsum = 0.f;
+          use = time_it([&] { return launch_conv_patch(out->pp, num_sms_, stream); }, &ms_patch) &&
+                time_it([&] { return launch_conv_tsum(ts, num_sms_, stream); }, &ms_tsum) &&
+                ms_tsum < ms_patch * 0.97f;
+          cudaEventDestroy(e1);
+        }
+        cudaEventDestroy(e0);
+      }
+      if (use) {
+        out->patch = false;
+        out->tsum = true;
+        out->ts = ts;
+      }
+    }
+    return true;
   }
   if (!tune) {
     // no timing (a batch size nobody prepared): the tap kernel with the traffic model's cluster
@@ -766,6 +815,7 @@ cudaError_t R2P1DModel::launch_one(const std::vector<Launch>& plan, size_t i,
   if (l.dual_n_sp > 0 && i + 1 < plan.size())
     return launch_conv_patch_dual(l.pp, plan[i + 1].pp, l.dual_n_sp, l.dual_chunk, d_dual_flags_,
                                   max_batch_, num_sms_, stream);
+  if (l.tsum) return launch_conv_tsum(l.ts, num_sms_, stream);
   return l.patch ? launch_conv_patch(l.pp, num_sms_, stream) : launch_tc(l.tc, stream);
 }
 
@@ -930,10 +980,10 @@ bool R2P1DModel::load_cached_plan(const char* path, int batch, cudaStream_t stre
     if (sscanf(line, "plan %llx %d", &key, &n) != 2 || key != want || n != (int)ops_.size()) continue;
     found = true;
     for (int i = 0; i < n && found; ++i) {
-      int op = -1, patch = 0, cm = 1, cn = 1, ks = 0, bn = 0, pair = 0, tpatch = 0, dual = 0;
+      int op = -1, patch = 0, cm = 1, cn = 1, ks = 0, bn = 0, pair = 0, tpatch = 0, dual = 0, tsum = 0;
       if (!fgets(line, sizeof line, f) ||
-          sscanf(line, "%d %d %d %d %d %d %d %d %d", &op, &patch, &cm, &cn, &ks, &bn, &pair,
-                 &tpatch, &dual) < 7 ||
+          sscanf(line, "%d %d %d %d %d %d %d %d %d %d", &op, &patch, &cm, &cn, &ks, &bn, &pair,
+                 &tpatch, &dual, &tsum) < 7 ||
           op != i) {
         found = false;
         break;
@@ -954,6 +1004,7 @@ bool R2P1DModel::load_cached_plan(const char* path, int batch, cudaStream_t stre
       like.tc.pair = pair;
       like.pp.pair = pair;
       like.tc.tpatch = tpatch;
+      like.tsum = tsum != 0;
       std::string e;
       if (!plan_conv(i, 0, batch, false, stream, &like, &l, &e)) found = false;
       l.dual_n_sp = dual;
@@ -980,8 +1031,8 @@ void R2P1DModel::save_cached_plan(const char* path, int batch, const std::vector
   if (!f) return;
   fprintf(f, "plan %llx %d\n", (unsigned long long)plan_key(batch), (int)plan.size());
   for (const Launch& l : plan)
-    fprintf(f, "%d %d %d %d %d %d %d %d %d\n", l.op, l.patch ? 1 : 0, l.tc.cm, l.tc.cn, l.tc.ks,
-            l.tc.block_n, l.patch ? l.pp.pair : l.tc.pair, l.tc.tpatch, l.dual_n_sp);
+    fprintf(f, "%d %d %d %d %d %d %d %d %d %d\n", l.op, l.patch ? 1 : 0, l.tc.cm, l.tc.cn, l.tc.ks,
+            l.tc.block_n, l.patch ? l.pp.pair : l.tc.pair, l.tc.tpatch, l.dual_n_sp, l.tsum ? 1 : 0);
   fclose(f);
 }
 
@@ -1035,8 +1086,23 @@ const std::vector<R2P1DModel::Launch>* R2P1DModel::ensure_plan(int batch, cudaSt
   } else if (!derive_plan(batch, &plan, err)) {
     return nullptr;
   }
+  set_clip_order(&plan);
   plans_[batch] = std::move(plan);
   return &plans_[batch];
+}
+
+// Alternating clip order (ConvPatchParams::reverse): the 1 x k x k convolutions take the clips last
+// to first, the k x 1 x 1 convolutions (and the fused stem) first to last, so every patch launch
+// starts on the clips its predecessor wrote last, which are the ones still in L2.
+// RNB_B200_CLIP_ORDER=forward keeps every launch first-to-last.
+void R2P1DModel::set_clip_order(std::vector<Launch>* plan) const {
+  static const bool snake = [] {
+    const char* e = getenv("RNB_B200_CLIP_ORDER");
+    return !(e && e[0] == 'f');
+  }();
+  for (Launch& l : *plan)
+    if (l.patch && !l.stem_fused)
+      l.pp.reverse = snake && l.dual_n_sp == 0 && !l.merged && ops_[l.op].g.kh > 1 ? 1 : 0;
 }
 
 bool R2P1DModel::plan_entry(int batch, int op, int out[7]) const {
@@ -1045,13 +1111,15 @@ bool R2P1DModel::plan_entry(int batch, int op, int out[7]) const {
   for (const Launch& l : it->second)
     if (l.op == op) {
       out[0] = l.patch ? 2 : (l.tc.pair ? (l.tc.tpatch ? 5 : 4) : (l.tc.ks > 1 ? 3 : 1));
+      if (l.tsum) out[0] = 8;
       if (l.dual_n_sp > 0 || l.merged) out[0] = 6;
       if (l.stem_fused || (stem_fused_ && op < 2)) out[0] = 7;
-      out[1] = l.dual_n_sp > 0 ? l.dual_n_sp : (l.patch ? 1 : l.tc.cm);
-      out[2] = l.patch ? 1 : l.tc.cn;
-      out[3] = l.patch ? 0 : l.tc.ks;
-      out[4] = l.patch ? l.pp.block_n : l.tc.block_n;
-      out[5] = l.patch ? l.pp.pair : l.tc.pair;
+      const bool one = l.patch || l.tsum;  // single-CTA kernels without cluster / split-K shape
+      out[1] = l.dual_n_sp > 0 ? l.dual_n_sp : (one ? 1 : l.tc.cm);
+      out[2] = one ? 1 : l.tc.cn;
+      out[3] = one ? 0 : l.tc.ks;
+      out[4] = l.tsum ? kTsumN : (l.patch ? l.pp.block_n : l.tc.block_n);
+      out[5] = l.tsum ? 0 : (l.patch ? l.pp.pair : l.tc.pair);
       out[6] = tuned_.count(batch) ? 1 : 0;
       return true;
     }
@@ -1117,6 +1185,7 @@ int R2P1DModel::force_kernel(int batch, int op_index, int kind, int cm, int cn, 
     b.merged = true;
     plan[op_index] = a;
     plan[op_index + 1] = b;
+    set_clip_order(&plan);
     return RNB_OK;
   }
   // (pinning one half of a co-scheduled pair on its own dissolves the pair)
@@ -1132,6 +1201,7 @@ int R2P1DModel::force_kernel(int batch, int op_index, int kind, int cm, int cn, 
     case 3: like.tc.ks = ks; like.tc.block_n = block_n; break;
     case 4: like.tc.pair = 1; like.tc.block_n = block_n; break;
     case 5: like.tc.pair = 1; like.tc.tpatch = 1; like.tc.block_n = block_n; break;
+    case 8: like.tsum = true; break;
     default:
       if (err) *err = "force_kernel: unknown kernel kind " + std::to_string(kind);
       return RNB_EINVAL;
@@ -1143,12 +1213,14 @@ int R2P1DModel::force_kernel(int batch, int op_index, int kind, int cm, int cn, 
                   : kind == 2 ? (l.patch && l.pp.pair == like.pp.pair)
                   : kind == 3 ? (!l.patch && l.tc.ks == ks && ks > 1)
                   : kind == 4 ? (!l.patch && l.tc.pair && !l.tc.tpatch)
+                  : kind == 8 ? l.tsum
                               : (!l.patch && l.tc.pair && l.tc.tpatch);
   if (!ok) {
     if (err) *err = ops_[op_index].name + ": the requested kernel shape does not apply to this layer";
     return RNB_EINVAL;
   }
   plan[op_index] = l;
+  set_clip_order(&plan);
   return RNB_OK;
 }
 

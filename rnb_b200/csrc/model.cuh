@@ -125,12 +125,16 @@ class R2P1DModel {
     // `merged`.
     bool stem_fused = false;
     StemFusedParams sf = {};
+    // taps-along-N temporal kernel (conv_tsum.cuh) instead of the patch kernel
+    bool tsum = false;
+    ConvTsumParams ts = {};
     int dual_n_sp = 0;   // > 0: CTAs that start on the spatial convolution
     int dual_chunk = 0;  // temporal items per claim
     bool merged = false;
   };
   bool plan_stem(int batch, std::vector<Launch>* plan, std::string* err);
   bool dual_candidate(const std::vector<Launch>& plan, int i) const;
+  void set_clip_order(std::vector<Launch>* plan) const;
   bool tune_dual(std::vector<Launch>* plan, int i, cudaStream_t stream);
   cudaError_t launch_one(const std::vector<Launch>& plan, size_t i, cudaStream_t stream) const;
   bool plan_conv(int op_index, int first, int batch, bool chunked, cudaStream_t stream,

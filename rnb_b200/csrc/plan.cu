@@ -821,4 +821,81 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
   return true;
 }
 
+// ---- temporal convolution with the taps along N (conv_tsum.cuh)
+bool conv_tsum_applicable(const ConvGeom& g) {
+  const int cp = g.cin_pad(), tail = cp % 64;
+  return !g.stem_unfolded && g.kt == 3 && g.kh == 1 && g.kw == 1 && g.st == 1 && g.sh == 1 &&
+         g.sw == 1 && g.pt == 1 && g.ph == 0 && g.pw == 0 && g.Ti == kTsumT && g.To == kTsumT &&
+         g.cout_pad() == kTsumCout && g.extra_cin == 0 && g.ncat == 0 &&
+         (g.in_pitch == 0 || g.in_pitch == cp) && cp <= kTsumMaxKb * 64 &&
+         (tail == 0 || tail == 16 || tail == 32 || cp + (64 - tail) <= kTsumMaxKb * 64);
+}
+
+bool build_conv_tsum_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
+                            const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
+                            const __nv_bfloat16* residual, bool relu, ConvTsumParams* out,
+                            std::string* err) {
+  if (!conv_tsum_applicable(g)) {
+    if (err) *err = "conv_tsum: geometry not supported";
+    return false;
+  }
+  ConvTsumParams& p = *out;
+  memset(&p, 0, sizeof p);
+  const int cp = g.cin_pad();
+  const int tail = cp % 64;
+  // 48 trailing channels: a zero-filled 64-channel block (the tensor map's bound) instead of a tail
+  p.tail_ch = (tail == 16 || tail == 32) ? tail : 0;
+  p.nkb = p.tail_ch ? cp / 64 : ceil_div(cp, 64);
+  p.cin_pad = cp;
+  p.HW = g.Ho * g.Wo;
+  p.tiles_hw = ceil_div(p.HW, kTsumPos);
+  p.B = B;
+  p.shift = shift;
+  p.residual = residual;
+  p.y = y;
+  p.relu = relu ? 1 : 0;
+  p.r_bufs = residual ? 3 : 0;
+  p.p_bufs = 6;
+  while (p.p_bufs > 2 && conv_tsum_smem_bytes(p.nkb, p.tail_ch, p.p_bufs, p.r_bufs) > kSmemLimit)
+    --p.p_bufs;
+  if (conv_tsum_smem_bytes(p.nkb, p.tail_ch, p.p_bufs, p.r_bufs) > kSmemLimit) {
+    if (err) *err = "conv_tsum: does not fit in shared memory";
+    return false;
+  }
+  {
+    const uint64_t hw = (uint64_t)p.HW, c2 = (uint64_t)cp * 2;
+    const uint64_t dims[5] = {(uint64_t)cp, (uint64_t)kTsumT, hw, (uint64_t)B, 1};
+    const uint64_t strides[4] = {hw * c2, c2, (uint64_t)kTsumT * hw * c2,
+                                 (uint64_t)B * kTsumT * hw * c2};
+    const uint32_t box[5] = {64u, (uint32_t)kTsumT, (uint32_t)kTsumPos, 1u, 1u};
+    if (!encode_bf16(&p.a_map, x, 5, dims, strides, box, 128, err)) return false;
+    p.r_map = p.a_map;
+    if (residual) {
+      const uint64_t o2 = (uint64_t)kTsumCout * 2;
+      const uint64_t rdims[5] = {(uint64_t)kTsumCout, (uint64_t)kTsumT, hw, (uint64_t)B, 1};
+      const uint64_t rstrides[4] = {hw * o2, o2, (uint64_t)kTsumT * hw * o2,
+                                    (uint64_t)B * kTsumT * hw * o2};
+      if (!encode_bf16(&p.r_map, residual, 5, rdims, rstrides, box, 128, err)) return false;
+    }
+    p.a_map_tail = p.a_map;
+    if (p.tail_ch) {
+      const uint32_t tbox[5] = {(uint32_t)p.tail_ch, (uint32_t)kTsumT, (uint32_t)kTsumPos, 1u, 1u};
+      if (!encode_bf16(&p.a_map_tail, x, 5, dims, strides, tbox, p.tail_ch * 2, err)) return false;
+    }
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)g.k_total(), (uint64_t)kTsumCout};
+    const uint64_t strides[1] = {(uint64_t)g.k_total() * 2};
+    const uint32_t box[2] = {64u, (uint32_t)kTsumCout};
+    if (!encode_bf16(&p.b_map, w_packed, 2, dims, strides, box, 128, err)) return false;
+    p.b_map_tail = p.b_map;
+    if (p.tail_ch) {
+      const uint32_t tbox[2] = {(uint32_t)p.tail_ch, (uint32_t)kTsumCout};
+      if (!encode_bf16(&p.b_map_tail, w_packed, 2, dims, strides, tbox, p.tail_ch * 2, err))
+        return false;
+    }
+  }
+  return true;
+}
+
 }  // namespace rnb

@@ -7,6 +7,7 @@
 #include "conv_patch.cuh"
 #include "conv_stem.cuh"
 #include "conv_tc.cuh"
+#include "conv_tsum.cuh"
 
 namespace rnb {
 
@@ -101,6 +102,14 @@ bool build_conv_patch_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
                              const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
                              const __nv_bfloat16* residual, bool relu, ConvPatchParams* out,
                              std::string* err, int pair = 0);
+
+// Temporal 3x1x1 convolution with the taps stacked along N and summed in the epilogue
+// (conv_tsum.cuh): 8-frame clips, 64 output channels, weights resident.
+bool conv_tsum_applicable(const ConvGeom& g);
+bool build_conv_tsum_params(const ConvGeom& g, int B, const __nv_bfloat16* x,
+                            const __nv_bfloat16* w_packed, __nv_bfloat16* y, const float* shift,
+                            const __nv_bfloat16* residual, bool relu, ConvTsumParams* out,
+                            std::string* err);
 
 // Fused stem (conv_stem.cuh).  Spatial weights: torch (cout, 3, 1, 7, 7) fp32 -> K-major bf16 rows
 // (96, 256), K = (4x4 tap of the space-to-depth filter) x 16 channel slots, rows scaled by the

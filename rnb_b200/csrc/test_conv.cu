@@ -292,6 +292,70 @@ static bool run_case(const Case& c, int perf_iters) {
     patch_pass = all_ok;
   }
 
+  // ---- the taps-along-N temporal kernel (conv_tsum.cu) on the same problem
+  if (conv_tsum_applicable(g)) {
+    ConvTsumParams ts;
+    bool ok = false;
+    if (!build_conv_tsum_params(g, B, dxb, dwp, dyb, dshift, drb, c.relu, &ts, &err)) {
+      printf("    tsum PLAN FAILED: %s\n", err.c_str());
+    } else {
+      for (int rev = 0; rev < 2; ++rev) {
+        ts.reverse = rev;
+        CK(cudaMemset(dyb, 0xff, out_pos * np * 2));
+        CK(launch_conv_tsum(ts, num_sms, 0));
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemcpy(yb.data(), dyb, yb.size() * 2, cudaMemcpyDeviceToHost));
+        double perr = 0;
+        size_t pbad = 0, nanc = 0;
+        for (size_t i = 0; i < out_pos; ++i)
+          for (int ch = 0; ch < np; ++ch) {
+            const float t = bf16_bits_to_f32(yb[i * np + ch]);
+            if (ch >= g.cout) {
+              if (t != 0.f) ++pbad;
+              continue;
+            }
+            const double e = fabs((double)t - yr[i * g.cout + ch]);
+            if (!(e == e)) ++nanc;
+            if (!(e <= perr)) perr = e;
+          }
+        ok = perr / (max_ref > 0 ? max_ref : 1) < 1e-2 && pbad == 0 && nanc == 0;
+        printf("    tsum kernel (nkb %d, tail %d, %d+%d bufs, reverse %d): max|err|=%.4f pad_bad=%zu nan=%zu  %s\n",
+               ts.nkb, ts.tail_ch, ts.p_bufs, ts.r_bufs, rev, perr, pbad, nanc, ok ? "PASS" : "FAIL");
+        if (!ok) break;
+      }
+      ts.reverse = 0;
+      if (ok && perf_iters > 0) {
+        cudaEvent_t e0, e1;
+        CK(cudaEventCreate(&e0));
+        CK(cudaEventCreate(&e1));
+        for (int i = 0; i < 3; ++i) CK(launch_conv_tsum(ts, num_sms, 0));
+        CK(cudaEventRecord(e0));
+        for (int i = 0; i < perf_iters; ++i) CK(launch_conv_tsum(ts, num_sms, 0));
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        const double us = ms * 1e3 / perf_iters;
+        printf("    tsum perf: %.1f us  %.1f TFLOP/s\n", us, g.flops(B) / us * 1e-6);
+#ifdef RNB_PATCH_COUNTERS
+        for (int dbg : {1, 2, 3, 4, 6, 7, 8, 9, 15}) {
+          ts.dbg = dbg;
+          for (int i = 0; i < 3; ++i) CK(launch_conv_tsum(ts, num_sms, 0));
+          CK(cudaEventRecord(e0));
+          for (int i = 0; i < perf_iters; ++i) CK(launch_conv_tsum(ts, num_sms, 0));
+          CK(cudaEventRecord(e1));
+          CK(cudaEventSynchronize(e1));
+          CK(cudaEventElapsedTime(&ms, e0, e1));
+          printf("      tsum ablation %2d (1 L2 input, 2 no stores, 4 no epilogue math, 8 no MMA): %.1f us\n",
+                 dbg, ms * 1e3 / perf_iters);
+        }
+        ts.dbg = 0;
+#endif
+      }
+    }
+    patch_pass = patch_pass && ok;
+  }
+
   if (perf_iters > 0 && pass) {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));

@@ -197,7 +197,7 @@ class R2P1DEngine:
         return self
 
     KERNEL_KINDS = ('conv_ref', 'conv_tc', 'conv_patch', 'conv_splitk', 'conv_pair', 'conv_tpatch',
-                    'conv_patch_dual', 'conv_stem_fused')
+                    'conv_patch_dual', 'conv_stem_fused', 'conv_tsum')
 
     def force_kernel(self, batch, op, kind, cm=0, cn=0, ks=0, block_n=0, pair=0):
         """Pin the kernel of convolution ``op`` at ``batch`` clips (tests and sweeps).  ``kind`` is a

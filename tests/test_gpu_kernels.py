@@ -72,6 +72,9 @@ VARIANTS = [
     ('dual-conv2', (2, 2), 3, 'spatial_conv', 'conv_patch_dual', dict(cm=100, cn=4)),
     ('dual-conv2-few-spatial', (2, 2), 2, 'spatial_conv', 'conv_patch_dual', dict(cm=20, cn=1)),
     ('dual-stem', (1, 1), 3, 'spatial_conv', 'conv_patch_dual', dict(cm=0, cn=0)),
+    # 3x1x1 layers with the filter taps stacked along the output columns and summed in the epilogue
+    ('tsum-conv2', (2, 2), 3, 'temporal_conv', 'conv_tsum', dict()),
+    ('tsum-stem', (1, 1), 2, 'temporal_conv', 'conv_tsum', dict()),
 ]
 
 

@@ -31,6 +31,8 @@ for rep in range(5):
     torch.cuda.synchronize()
     us = e0.elapsed_time(e1) / args.iters * 1e3
     best = us if best is None else min(best, us)
+kinds = [eng.plan_entry(B, i)[0] for i in range(eng.num_convs)]
+print('kernels:', ' '.join('%d:%s' % (i, k.replace('conv_', '')) for i, k in enumerate(kinds)))
 print('%s batch %d: %.1f us/step  %.0f clips/s  launches %d  env %s' % (
     args.model, B, best, B / best * 1e6, eng.num_launches,
     {k: v for k, v in os.environ.items() if k.startswith('RNB_B200')}))

@@ -20,6 +20,8 @@ def main():
     ap.add_argument('--batch', type=int, default=16)
     ap.add_argument('--model', default='r18')
     ap.add_argument('--steps', type=int, default=30)
+    ap.add_argument('--raw', action='store_true',
+                    help='launch list without layer names (chunked schedules: RNB_B200_CHUNK_MB)')
     args = ap.parse_args()
     import torch
     from rnb_b200 import cupti
@@ -46,6 +48,8 @@ def main():
     names, flops = ['input staging'], [0.0]
     info = eng.op_info()
     k = 0
+    if args.raw:
+        names, flops, info = ['-'] * n, [0.0] * n, []
     while k < len(info):
         nm, f, _, _, kind = info[k]
         if kind in ('conv_patch_dual', 'conv_stem_fused') and k + 1 < len(info) \
@@ -57,8 +61,9 @@ def main():
             names.append(nm)
             flops.append(f * B)
             k += 1
-    names.append('pool + classifier')
-    flops.append(0.0)
+    if not args.raw:
+        names.append('pool + classifier')
+        flops.append(0.0)
     dur = [0.0] * n
     exp = [0.0] * n
     gap = [0.0] * n
