@@ -557,7 +557,18 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
   const bool patch_only = patch_ok && !conv_patch_streams(op.g);
   if (patch_only) {
     out->patch = true;
-    if (!build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &out->pp, &perr))
+    // RNB_B200_PATCH_PAIR=1 (measurements only): the CTA-pair form of the resident patch kernel on
+    // the 1 x k x k layers it applies to
+    static const bool want_pair = [] {
+      const char* e = getenv("RNB_B200_PATCH_PAIR");
+      return e && e[0] == '1';
+    }();
+    const int pair = want_pair && op.g.kh > 1 && conv_patch_applicable(op.g, 1) &&
+                             !conv_patch_streams(op.g, 1)
+                         ? 1
+                         : 0;
+    if (!build_conv_patch_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, &out->pp, &perr,
+                                 pair))
       return fail(perr);
     // 3x1x1 layers of 8-frame clips: the taps-along-N kernel (conv_tsum.cuh).  Measured equal to
     // the patch kernel within 1-2 % in the real step (profiles/r02_conv_tsum.md: both designs load
