@@ -68,6 +68,9 @@ VARIANTS = [
     ('splitk-3', (5, 5), 16, 'conv', 'conv_splitk', dict(ks=3, block_n=128)),
     ('splitk-4', (4, 4), 16, 'conv', 'conv_splitk', dict(ks=4, block_n=128)),
     ('splitk-2-conv3', (3, 3), 4, 'spatial_conv', 'conv_splitk', dict(ks=2, block_n=256)),
+    ('splitk-8', (5, 5), 2, 'conv', 'conv_splitk', dict(ks=8, block_n=128)),
+    ('splitk-8-narrow', (5, 5), 1, 'spatial_conv', 'conv_splitk', dict(ks=8, block_n=64)),
+    ('splitk-6-conv4', (4, 4), 1, 'conv', 'conv_splitk', dict(ks=6, block_n=128)),
     # one co-scheduled launch per SpatioTemporalConv (spatial CTAs + temporal CTAs, per-clip counters)
     ('dual-conv2', (2, 2), 3, 'spatial_conv', 'conv_patch_dual', dict(cm=100, cn=4)),
     ('dual-conv2-few-spatial', (2, 2), 2, 'spatial_conv', 'conv_patch_dual', dict(cm=20, cn=1)),
