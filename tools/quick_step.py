@@ -31,8 +31,10 @@ for rep in range(5):
     torch.cuda.synchronize()
     us = e0.elapsed_time(e1) / args.iters * 1e3
     best = us if best is None else min(best, us)
-kinds = [eng.plan_entry(B, i)[0] for i in range(eng.num_convs)]
-print('kernels:', ' '.join('%d:%s' % (i, k.replace('conv_', '')) for i, k in enumerate(kinds)))
+ents = [eng.plan_entry(B, i) for i in range(eng.num_convs)]
+print('kernels:', ' '.join('%d:%s%s' % (i, e[0].replace('conv_', ''),
+                                        ('(ks%d,n%d)' % (e[1]['ks'], e[1]['block_n'])) if e[0] == 'conv_splitk' else '')
+                           for i, e in enumerate(ents)))
 print('%s batch %d: %.1f us/step  %.0f clips/s  launches %d  env %s' % (
     args.model, B, best, B / best * 1e6, eng.num_launches,
     {k: v for k, v in os.environ.items() if k.startswith('RNB_B200')}))
