@@ -270,3 +270,19 @@ def test_harness_topologies_are_valid_pipelines():
                 assert set(g['in_queue'] for g in step['queue_groups']) == out_queues
             if i < len(cfg['pipeline']) - 1:
                 out_queues = set(q for g in step['queue_groups'] for q in g['out_queues'])
+
+
+def test_kernel_kind_names_match_the_header():
+    """engine.KERNEL_KINDS[k] is the name of kind k of rnb_r2p1d_op_info / force_kernel (include/rnb_b200.h)."""
+    import re
+    from rnb_b200.engine import R2P1DEngine
+    header = open(os.path.join(os.path.dirname(__file__), '..', 'include', 'rnb_b200.h')).read()
+    doc = re.sub(r'\s*\n \*\s*', ' ', header[header.index('rnb_r2p1d_op_info() describes'):])
+    for k, name in enumerate(R2P1DEngine.KERNEL_KINDS):
+        if k == 0:
+            assert '0 = fp32 direct convolution' in doc
+            continue
+        m = re.search(r'\b%d = (\w+)' % k, doc)
+        assert m, 'kind %d is not documented in the header' % k
+        kernel = m.group(1)          # e.g. conv_pair_kernel
+        assert kernel.startswith(name.replace('conv_tpatch', 'conv_pair')), (k, name, kernel)
