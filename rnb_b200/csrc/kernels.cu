@@ -189,52 +189,73 @@ to_stem_kernel(const In* __restrict__ in, int total_rows, Affine3 aff, uint4* __
 
 // Space-to-depth stem input for the fused stem kernel (conv_stem.cuh): (B, 8, 56, 56, 16) bf16,
 // channel (py * 2 + px) * 4 + c = pixel (2 h2 + py, 2 w2 + px) of colour c; slot 3 is zero except
-// for pixel (0, 0), where it holds the constant 1 (conv_stem.cuh).  One CTA
-// per (b, t, h2): the two image rows of the three colours are read coalesced into shared memory,
-// then every thread writes one 16-byte unit (row py of one output position).
+// for pixel (0, 0), where it holds the constant 1 (conv_stem.cuh).  One thread per four pixels of a
+// row pair: six coalesced 4-pixel loads (three colours, two rows), all in flight together, and 64
+// contiguous bytes out (two output positions x two rows); no shared memory, no barrier.
 template <typename In>
 __global__ void __launch_bounds__(128)
-to_s2d_kernel(const In* __restrict__ in, int total_rows2, Affine3 aff, uint4* __restrict__ out,
+to_s2d_kernel(const In* __restrict__ in, long long total_quads, Affine3 aff, uint4* __restrict__ out,
               bool ncdhw) {
-  __shared__ float px[2][kClipC][kClipW];
+  constexpr int kQuads = kClipW / 4;  // 4-pixel groups per row
   ptx::grid_dep_launch_dependents();
-  ptx::grid_dep_wait();  // the buffer this kernel overwrites may be an operand of the previous kernel
-  for (int r2 = blockIdx.x; r2 < total_rows2; r2 += gridDim.x) {  // r2 = (b * T + t) * 56 + h2
-  if (r2 != (int)blockIdx.x) __syncthreads();  // the previous row pair has been read out
-  const int h2 = r2 % (kClipH / 2);
-  const int bt = r2 / (kClipH / 2);
-  const int t = bt % kClipT;
-  const long long b = bt / kClipT;
-  for (int i = threadIdx.x; i < 2 * kClipC * (kClipW / 4); i += blockDim.x) {
-    const int q = i % (kClipW / 4);
-    const int c = (i / (kClipW / 4)) % kClipC;
-    const int py = i / (kClipC * (kClipW / 4));
-    const int h = 2 * h2 + py;
-    const long long base = ncdhw ? ((((b * kClipC + c) * kClipT + t) * kClipH + h) * (long long)kClipW)
-                                 : ((((b * kClipT + t) * kClipC + c) * kClipH + h) * (long long)kClipW);
-    float v[4];
-    if (sizeof(In) == 1) {
-      const uchar4 u = *reinterpret_cast<const uchar4*>(in + base + 4 * q);
-      v[0] = u.x; v[1] = u.y; v[2] = u.z; v[3] = u.w;
-    } else {
-      const float4 f = *reinterpret_cast<const float4*>(in + base + 4 * q);
-      v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
-    }
+  bool waited = false;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total_quads;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int q = (int)(i % kQuads);
+    const long long r2 = i / kQuads;  // (b * T + t) * 56 + h2
+    const int h2 = (int)(r2 % (kClipH / 2));
+    const long long bt = r2 / (kClipH / 2);
+    const int t = (int)(bt % kClipT);
+    const long long b = bt / kClipT;
+    float v[2][kClipC][4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) px[py][c][4 * q + j] = fmaf(v[j], aff.s[c], aff.b[c]);
+    for (int py = 0; py < 2; ++py)
+#pragma unroll
+      for (int c = 0; c < kClipC; ++c) {
+        const int h = 2 * h2 + py;
+        const long long base =
+            ncdhw ? ((((b * kClipC + c) * kClipT + t) * kClipH + h) * (long long)kClipW)
+                  : ((((b * kClipT + t) * kClipC + c) * kClipH + h) * (long long)kClipW);
+        if (sizeof(In) == 1) {
+          const uchar4 u = *reinterpret_cast<const uchar4*>(in + base + 4 * q);
+          v[py][c][0] = u.x; v[py][c][1] = u.y; v[py][c][2] = u.z; v[py][c][3] = u.w;
+        } else {
+          const float4 f = *reinterpret_cast<const float4*>(in + base + 4 * q);
+          v[py][c][0] = f.x; v[py][c][1] = f.y; v[py][c][2] = f.z; v[py][c][3] = f.w;
+        }
+      }
+    // The frames are read before the wait: no kernel of this library that lets its successor start
+    // early (programmatic dependent launch) writes frame tensors, and anything else in the stream
+    // has completed before this grid starts.  The output buffer may still be an operand of the
+    // previous forward's kernels, so the stores come after it.
+    if (!waited) {
+      ptx::grid_dep_wait();
+      waited = true;
+    }
+    uint4 o[4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)      // output position w2 = 2 q + j
+#pragma unroll
+      for (int py = 0; py < 2; ++py) {
+        float a[kClipC][2];
+#pragma unroll
+        for (int c = 0; c < kClipC; ++c) {
+          a[c][0] = fmaf(v[py][c][2 * j], aff.s[c], aff.b[c]);
+          a[c][1] = fmaf(v[py][c][2 * j + 1], aff.s[c], aff.b[c]);
+        }
+        uint4 u;
+        u.x = pack2(a[0][0], a[1][0]);
+        // slot 3 of pixel (py, px) = (0, 0): the constant one that carries the BatchNorm shift
+        u.y = pack2(a[2][0], py == 0 ? 1.f : 0.f);
+        u.z = pack2(a[0][1], a[1][1]);
+        u.w = pack2(a[2][1], 0.f);
+        o[2 * j + py] = u;
+      }
+    uint4* dst = out + (r2 * (kClipW / 2) + 2 * q) * 2;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) dst[k] = o[k];
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < (kClipW / 2) * 2; i += blockDim.x) {
-    const int w2 = i >> 1, py = i & 1;
-    uint4 q;
-    q.x = pack2(px[py][0][2 * w2], px[py][1][2 * w2]);
-    // slot 3 of pixel (py, px) = (0, 0): the constant one that carries the BatchNorm shift
-    q.y = pack2(px[py][2][2 * w2], py == 0 ? 1.f : 0.f);
-    q.z = pack2(px[py][0][2 * w2 + 1], px[py][1][2 * w2 + 1]);
-    q.w = pack2(px[py][2][2 * w2 + 1], 0.f);
-    out[((long long)r2 * (kClipW / 2) + w2) * 2 + py] = q;
-  }
-  }
+  if (!waited) ptx::grid_dep_wait();
 }
 
 // uint8 (B,T,C,H,W) -> fp32 (B,C,T,H,W); four pixels per thread
@@ -558,22 +579,24 @@ cudaError_t launch_f32_ncdhw_to_stem(const float* in, int batch, __nv_bfloat16* 
                     nullptr, 0, in, rows, make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
 }
 
-// grid of the space-to-depth staging kernel: a few row pairs per CTA once there are many
-static inline int s2d_grid(int rows2) { return rows2; }  // (several row pairs per CTA: slower)
+// grid of the space-to-depth staging kernel: one thread per 4-pixel group of a row pair
+static inline int s2d_grid(long long quads) { return (int)((quads + 127) / 128); }
 
 cudaError_t launch_pre_u8_to_s2d(const uint8_t* in, int batch, const float* scale3,
                                  const float* bias3, __nv_bfloat16* out, cudaStream_t s) {
   const int rows2 = batch * kClipT * (kClipH / 2);
   if (rows2 == 0) return cudaSuccess;
-  return launch_pdl(to_s2d_kernel<uint8_t>, dim3(s2d_grid(rows2)), dim3(128), 0, s, out,
-                    (size_t)rows2 * (kClipW / 2) * 32, in, rows2, make_affine(scale3, bias3),
+  const long long quads = (long long)rows2 * (kClipW / 4);
+  return launch_pdl(to_s2d_kernel<uint8_t>, dim3(s2d_grid(quads)), dim3(128), 0, s, out,
+                    (size_t)rows2 * (kClipW / 2) * 32, in, quads, make_affine(scale3, bias3),
                     reinterpret_cast<uint4*>(out), false);
 }
 
 cudaError_t launch_f32_ncdhw_to_s2d(const float* in, int batch, __nv_bfloat16* out, cudaStream_t s) {
   const int rows2 = batch * kClipT * (kClipH / 2);
   if (rows2 == 0) return cudaSuccess;
-  return launch_pdl(to_s2d_kernel<float>, dim3(s2d_grid(rows2)), dim3(128), 0, s, nullptr, 0, in, rows2,
+  const long long quads = (long long)rows2 * (kClipW / 4);
+  return launch_pdl(to_s2d_kernel<float>, dim3(s2d_grid(quads)), dim3(128), 0, s, nullptr, 0, in, quads,
                     make_affine(nullptr, nullptr), reinterpret_cast<uint4*>(out), true);
 }
 
