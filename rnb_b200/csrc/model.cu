@@ -711,10 +711,10 @@ bool R2P1DModel::plan_conv(int op_index, int first, int batch, bool chunked, cud
   if (allow_splitk && !failed && ok && !out->patch) {
     // (the 6- and 8-way splits and the 64-wide tiles only ever win at one to three clips, where a
     // conv4 / conv5 layer has a single position tile: per-video latency of the 1-clip videos)
-    static const int sk_cand[9][2] = {{2, 256}, {3, 256}, {2, 128}, {3, 128}, {4, 128},
-                                      {6, 128}, {8, 128}, {4, 64},  {8, 64}};
+    static const int sk_cand[10][2] = {{2, 256}, {3, 256}, {2, 128}, {3, 128}, {4, 128},
+                                       {6, 128}, {8, 128}, {2, 64},  {4, 64},  {8, 64}};
     const int tap_items = out->tc.m_tiles * out->tc.n_tiles;
-    for (int ci = 0; ci < 9 && !failed; ++ci) {
+    for (int ci = 0; ci < 10 && !failed; ++ci) {
       ConvTcParams trial;
       std::string serr;
       if (!build_conv_tc_params(op.g, batch, x, w, y, op.d_shift, res, op.relu, num_sms_, &trial,
